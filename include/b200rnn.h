@@ -1,0 +1,142 @@
+/*
+ * b200rnn — C ABI of the B200-native (sm_100a) RNN training kernels.
+ *
+ * Every entry point takes raw device pointers plus a CUDA stream (passed as
+ * void* so this header needs no CUDA include) and returns 0 on success or a
+ * negative B200RNN_E* code; b200rnn_last_error() gives the message.
+ * None of the functions in this header allocate device memory unless their
+ * comment says so: the caller (the Python package, through torch's caching
+ * allocator) owns all buffers and sizes them with the *_floats() queries.
+ *
+ * Parity citations are paths into the reference tree (jkhlr/pytorch-distributed-rnn).
+ */
+#ifndef B200RNN_H_
+#define B200RNN_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200RNN_MAX_LAYERS 8
+#define B200RNN_MAX_PEERS 16
+
+enum {
+  B200RNN_OK = 0,
+  B200RNN_EINVAL = -1,      /* bad argument / unsupported shape */
+  B200RNN_ECUDA = -2,       /* a CUDA call failed */
+  B200RNN_EUNSUPPORTED = -3,/* shape not covered by this kernel family */
+  B200RNN_ETOOBIG = -4,     /* request exceeds a fixed capacity */
+  B200RNN_ESYS = -5         /* OS / socket error (runtime bootstrap) */
+};
+
+enum { B200RNN_CELL_LSTM = 0, B200RNN_CELL_GRU = 1 };
+
+/* Model geometry + where each parameter lives inside the flat fp32 arena.
+ * Parameter order and shapes are torch.nn.LSTM's (src/motion/model.py:9-10):
+ * weight_ih_l{k} [G*H, in], weight_hh_l{k} [G*H, H], bias_ih_l{k} [G*H],
+ * bias_hh_l{k} [G*H] (G = 4 gates i,f,g,o for LSTM; 3 gates r,z,n for GRU),
+ * then the optional classifier head fc.weight [C, H], fc.bias [C]. */
+typedef struct {
+  int32_t cell;          /* B200RNN_CELL_* */
+  int32_t input_size;    /* I */
+  int32_t hidden_size;   /* H */
+  int32_t num_layers;    /* L <= B200RNN_MAX_LAYERS */
+  int32_t batch;         /* B (per rank) */
+  int32_t seq_len;       /* T */
+  int32_t num_classes;   /* C, 0 = no head */
+  int32_t reserved;
+  int64_t off_wih[B200RNN_MAX_LAYERS];
+  int64_t off_whh[B200RNN_MAX_LAYERS];
+  int64_t off_bih[B200RNN_MAX_LAYERS];
+  int64_t off_bhh[B200RNN_MAX_LAYERS];
+  int64_t off_fcw;
+  int64_t off_fcb;
+  int64_t n_params;      /* arena length in floats (gradient rows carry 2 extra slots) */
+} b200rnn_model_desc;
+
+const char* b200rnn_last_error(void);
+int b200rnn_version(void);
+
+/* ---- K11: device-resident dataset gather (replaces DataLoader collate,
+ * src/motion/trainer/base.py:56-60,107).  x_out[b] = feats[idx[b]] (row_elems
+ * floats per row), y_out[b] = labels[idx[b]]. */
+int b200rnn_gather_batch(const float* feats, const int64_t* labels,
+                         const int64_t* idx, int32_t batch, int32_t row_elems,
+                         float* x_out, int64_t* y_out, void* stream);
+
+/* ---- K2/K3: fused persistent recurrent kernels, small-hidden family
+ * (whole sequence, all layers, one launch; recurrent weights register-resident).
+ * Replaces ATen lstm fwd/bwd (src/motion/model.py:14, trainer/base.py:116). */
+
+/* 1 if (cell, I, H, L) is covered by the fused small-hidden family. */
+int b200rnn_rnn_small_supported(const b200rnn_model_desc* d);
+/* Batch rows per CTA and CTA count the fused kernels will use for d->batch. */
+int b200rnn_rnn_small_tiling(const b200rnn_model_desc* d, int32_t* rows_per_cta, int32_t* n_cta);
+/* Activation stash written by forward (training=1) and read by backward. */
+int64_t b200rnn_rnn_stash_floats(const b200rnn_model_desc* d);
+/* Backward scratch: per-CTA gradient partial rows + inter-layer dx buffers. */
+int64_t b200rnn_rnn_bwd_scratch_floats(const b200rnn_model_desc* d);
+/* Length of one gradient row: n_params + 2 (loss sum, correct count). */
+int64_t b200rnn_grad_row_floats(const b200rnn_model_desc* d);
+
+/* x [B,T,I] fp32 contiguous. stash layout (floats):
+ *   h_seq [L][T][B][H] | c_seq [L][T][B][H] | gates [L][T][B][H][4]
+ * (c_seq and gates only written when training != 0).  The top layer's
+ * h_seq[L-1] is the module output in time-major order. */
+int b200rnn_lstm_fwd(const b200rnn_model_desc* d, const float* params,
+                     const float* x, float* stash, int32_t training, void* stream);
+
+/* Backward through time for all layers.  Gradient sources (all optional):
+ *   labels != NULL && d->num_classes > 0: the classifier head + mean
+ *       cross-entropy + correct-count are evaluated in-kernel on
+ *       h_seq[L-1][T-1] (src/motion/model.py:16, trainer/base.py:112-114),
+ *       loss scaled by loss_scale (normally 1/B);
+ *   d_out  [B,T,H] gradient of the top layer's full output sequence;
+ *   d_hn / d_cn [L][B][H] gradients of the final hidden / cell states.
+ * Results: scratch holds n_cta partial gradient rows (row r = CTA r's
+ * contribution, b200rnn_grad_row_floats() long, torch parameter order, then
+ * [n_params] = sum of per-sample losses, [n_params+1] = correct count);
+ * reduce them with b200rnn_reduce_rows() or b200rnn_fused_update(). */
+int b200rnn_lstm_bwd(const b200rnn_model_desc* d, const float* params,
+                     const float* x, const float* stash, const int64_t* labels,
+                     float loss_scale, const float* d_out, const float* d_hn,
+                     const float* d_cn, float* scratch, void* stream);
+
+/* out[i] (+)= sum_r rows[r][i] in fixed row order (deterministic). */
+int b200rnn_reduce_rows(const float* rows, int32_t n_rows, int64_t row_floats,
+                        float* out, int32_t accumulate, void* stream);
+
+/* ---- K5: classifier head, standalone form (evaluation and autograd path).
+ * h_last [B,H] (row stride ld_h floats), logits out [B,C] (nullable),
+ * metrics out: [0] = sum of per-sample CE losses, [1] = correct count. */
+int b200rnn_head_fwd(const float* h_last, int64_t ld_h, const float* fc_w, const float* fc_b,
+                     const int64_t* labels, int32_t batch, int32_t hidden, int32_t classes,
+                     float* logits, float* metrics, void* stream);
+
+/* ---- K6: fused optimizers on the flat arena (src/motion/trainer/base.py:42-43,117;
+ * src/example/example_ddp.py:54,82). */
+typedef struct {
+  int32_t kind;        /* 0 = Adam, 1 = SGD */
+  int32_t step;        /* 1-based step number (Adam bias correction) */
+  float lr, beta1, beta2, eps, weight_decay, momentum;
+  float grad_scale;    /* multiplies the summed gradient (1/world for DDP mean) */
+  int32_t reserved;
+} b200rnn_optim_desc;
+
+/* grad = grad_scale * sum_r rows[r][i]; apply optimizer in place on
+ * params/exp_avg/exp_avg_sq; copy row tail (loss sum, correct) to metrics[2]
+ * (nullable); optionally also store the reduced gradient to grad_out (nullable). */
+int b200rnn_fused_update(const float* rows, int32_t n_rows, int64_t n_params,
+                         float* params, float* exp_avg, float* exp_avg_sq,
+                         const b200rnn_optim_desc* opt, float* grad_out,
+                         float* metrics, void* stream);
+
+/* ---- L2 flush helper for benchmarking (writes `bytes` of scratch). */
+int b200rnn_l2_flush(void* scratch, int64_t bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200RNN_H_ */

@@ -1,0 +1,131 @@
+"""ctypes binding of ``libb200rnn.so`` (C ABI in ``include/b200rnn.h``).
+
+The library is built in-tree by :mod:`._build` and loaded from
+``pytorch_distributed_rnn_b200/_lib``.  On a CUDA machine a missing or unloadable
+library is a hard error (no silent fallback to eager PyTorch); on a CPU-only
+machine the package works without it through the torch reference path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from typing import Optional
+
+import torch
+
+from . import _build
+
+MAX_LAYERS = 8
+MAX_PEERS = 16
+
+_lib: Optional[C.CDLL] = None
+_lib_err: Optional[str] = None
+_lock = threading.Lock()
+
+
+class ModelDesc(C.Structure):
+    _fields_ = [
+        ("cell", C.c_int32), ("input_size", C.c_int32), ("hidden_size", C.c_int32),
+        ("num_layers", C.c_int32), ("batch", C.c_int32), ("seq_len", C.c_int32),
+        ("num_classes", C.c_int32), ("reserved", C.c_int32),
+        ("off_wih", C.c_int64 * MAX_LAYERS), ("off_whh", C.c_int64 * MAX_LAYERS),
+        ("off_bih", C.c_int64 * MAX_LAYERS), ("off_bhh", C.c_int64 * MAX_LAYERS),
+        ("off_fcw", C.c_int64), ("off_fcb", C.c_int64), ("n_params", C.c_int64),
+    ]
+
+
+class OptimDesc(C.Structure):
+    _fields_ = [
+        ("kind", C.c_int32), ("step", C.c_int32),
+        ("lr", C.c_float), ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float),
+        ("weight_decay", C.c_float), ("momentum", C.c_float), ("grad_scale", C.c_float),
+        ("reserved", C.c_int32),
+    ]
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+def _declare(lib: C.CDLL) -> None:
+    vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
+    P = C.POINTER
+    lib.b200rnn_last_error.restype = C.c_char_p
+    lib.b200rnn_version.restype = i32
+    sigs = {
+        "b200rnn_gather_batch": (i32, [vp, vp, vp, i32, i32, vp, vp, vp]),
+        "b200rnn_rnn_small_supported": (i32, [P(ModelDesc)]),
+        "b200rnn_rnn_small_tiling": (i32, [P(ModelDesc), P(i32), P(i32)]),
+        "b200rnn_rnn_stash_floats": (i64, [P(ModelDesc)]),
+        "b200rnn_rnn_bwd_scratch_floats": (i64, [P(ModelDesc)]),
+        "b200rnn_grad_row_floats": (i64, [P(ModelDesc)]),
+        "b200rnn_lstm_fwd": (i32, [P(ModelDesc), vp, vp, vp, i32, vp]),
+        "b200rnn_lstm_bwd": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
+        "b200rnn_reduce_rows": (i32, [vp, i32, i64, vp, i32, vp]),
+        "b200rnn_head_fwd": (i32, [vp, i64, vp, vp, vp, i32, i32, i32, vp, vp, vp]),
+        "b200rnn_fused_update": (i32, [vp, i32, i64, vp, vp, vp, P(OptimDesc), vp, vp, vp]),
+        "b200rnn_l2_flush": (i32, [vp, i64, vp]),
+    }
+    for name, (res, args) in sigs.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+
+
+def load(required: bool = False) -> Optional[C.CDLL]:
+    """Load (building first if stale and nvcc is present) the native library."""
+    global _lib, _lib_err
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if _lib_err is None:
+            try:
+                if _build.is_stale() and _build.find_nvcc() is not None:
+                    _build.build()
+                lib = C.CDLL(str(_build.LIB_PATH))
+                _declare(lib)
+                _lib = lib
+                return _lib
+            except (OSError, RuntimeError, AttributeError) as e:  # missing nvcc / .so / symbol
+                _lib_err = f"{type(e).__name__}: {e}"
+        if required:
+            raise NativeError(
+                "libb200rnn.so is not available (%s). Build it with "
+                "`python -m pytorch_distributed_rnn_b200._build`." % _lib_err)
+        return None
+
+
+def available() -> bool:
+    return load() is not None
+
+
+def lib() -> C.CDLL:
+    return load(required=True)
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = lib().b200rnn_last_error().decode("utf-8", "replace")
+        raise NativeError(f"{what or 'b200rnn call'} failed (rc={rc}): {msg}")
+
+
+def ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    """Raw device pointer of a tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr(device: Optional[torch.device] = None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+# ---- launch accounting (bench.py reports it as "gpu_launches") ----
+_launches = 0
+
+
+def count_launch(n: int = 1) -> None:
+    global _launches
+    _launches += n
+
+
+def launches() -> int:
+    return _launches

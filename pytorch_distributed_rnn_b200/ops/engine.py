@@ -1,0 +1,145 @@
+"""FusedTrainEngine — the whole training step of the motion classifier as 3 kernel launches.
+
+The reference's hot loop (src/motion/trainer/base.py:103-130) is, per batch:
+``zero_grad -> model(data) -> CrossEntropyLoss -> argmax/eq/sum -> backward -> Adam.step``
+— hundreds of ATen kernel launches, two host syncs (``loss.item()`` twice) and, under DDP,
+a blocking all-reduce inside ``backward``.  Here the same step is:
+
+1. ``b200rnn_lstm_fwd``   — all layers, all timesteps, one persistent launch (K2);
+2. ``b200rnn_lstm_bwd``   — head + CE + correct-count + BPTT + dW accumulation (K5+K3+K4);
+3. ``b200rnn_fused_update`` (1 GPU) or ``b200rnn_comm_allreduce_update`` (N GPUs) —
+   deterministic reduction of the per-CTA gradient rows, the in-kernel NVLink all-reduce,
+   gradient averaging and the Adam/SGD step (K6+K7);
+
+plus an optional K11 gather in front when the batch comes from a device-resident dataset.
+Nothing in the step synchronises with the host; loss / correct-count land in a device ring
+buffer that the trainer reads when it wants to log.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional, Tuple
+
+import torch
+
+from .. import _native
+from .._native import ModelDesc
+from ..models.motion import MotionModel
+from ..utils.arena import ParamArena
+from .optim import FusedAdam, _FlatOptimizer
+from .rnn_function import CELL_ID
+
+
+class FusedTrainEngine:
+    METRIC_RING = 1024
+
+    def __init__(self, model: MotionModel, optimizer: Optional[_FlatOptimizer] = None, lr: float = 0.0025,
+                 arena: Optional[ParamArena] = None, comm=None):
+        p0 = next(model.parameters())
+        if not p0.is_cuda:
+            raise ValueError("FusedTrainEngine needs the model on a CUDA device")
+        self.lib = _native.lib()
+        self.model = model
+        self.device = p0.device
+        self.comm = comm
+        self.arena = arena if arena is not None else (optimizer.arena if optimizer is not None else ParamArena(model))
+        self.optimizer = optimizer if optimizer is not None else FusedAdam(self.arena, lr=lr)
+        self.world = 1 if comm is None else comm.world
+        self._bufs: Dict[Tuple[int, int], dict] = {}
+        self.metrics = torch.zeros(self.METRIC_RING, 2, dtype=torch.float32, device=self.device)
+        self.eval_metrics = torch.zeros(256, dtype=torch.float32, device=self.device)
+        self.n_steps = 0
+        d = self._desc(1, 1)
+        if not self.lib.b200rnn_rnn_small_supported(C.byref(d)):
+            raise NotImplementedError(
+                f"no fused kernel family covers cell={model.cell} I={model.input_dim} H={model.hidden_dim} "
+                f"L={model.layer_dim} C={model.output_dim}")
+
+    # -- descriptor with offsets taken from the arena --
+    def _desc(self, B: int, T: int) -> ModelDesc:
+        m, a = self.model, self.arena
+        d = ModelDesc()
+        d.cell = CELL_ID[m.cell]
+        d.input_size, d.hidden_size, d.num_layers = m.input_dim, m.hidden_dim, m.layer_dim
+        d.batch, d.seq_len, d.num_classes = B, T, m.output_dim
+        for l in range(m.layer_dim):
+            d.off_wih[l] = a.offset(f"lstm.weight_ih_l{l}")
+            d.off_whh[l] = a.offset(f"lstm.weight_hh_l{l}")
+            d.off_bih[l] = a.offset(f"lstm.bias_ih_l{l}")
+            d.off_bhh[l] = a.offset(f"lstm.bias_hh_l{l}")
+        d.off_fcw = a.offset("fc.weight")
+        d.off_fcb = a.offset("fc.bias")
+        d.n_params = a.numel
+        return d
+
+    def _get(self, B: int, T: int) -> dict:
+        key = (B, T)
+        buf = self._bufs.get(key)
+        if buf is None:
+            d = self._desc(B, T)
+            rb, nc = C.c_int32(), C.c_int32()
+            _native.check(self.lib.b200rnn_rnn_small_tiling(C.byref(d), C.byref(rb), C.byref(nc)), "tiling")
+            buf = dict(
+                desc=d, n_cta=nc.value, rows_per_cta=rb.value,
+                stash=torch.empty(self.lib.b200rnn_rnn_stash_floats(C.byref(d)), dtype=torch.float32, device=self.device),
+                scratch=torch.empty(self.lib.b200rnn_rnn_bwd_scratch_floats(C.byref(d)), dtype=torch.float32, device=self.device),
+                x=None, y=None)
+            self._bufs[key] = buf
+        return buf
+
+    # -- one optimisation step on a device batch --
+    def train_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """x [B,T,I] fp32, y [B] or [B,1] int64, both on the engine's device.
+        Returns a device view [2] = (sum of per-sample CE losses, correct count) for this batch."""
+        B, T, _ = x.shape
+        buf = self._get(B, T)
+        d = buf["desc"]
+        y = y.reshape(-1)
+        sp = _native.stream_ptr(self.device)
+        a, opt = self.arena, self.optimizer
+        _native.check(self.lib.b200rnn_lstm_fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 1, sp), "lstm_fwd")
+        _native.check(self.lib.b200rnn_lstm_bwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(),
+                                                y.data_ptr(), 1.0 / B, None, None, None, buf["scratch"].data_ptr(), sp), "lstm_bwd")
+        opt.step_count += 1
+        slot = self.metrics[self.n_steps % self.METRIC_RING]
+        o = opt.desc(grad_scale=1.0 / self.world)
+        if self.comm is None or self.world == 1:
+            _native.check(self.lib.b200rnn_fused_update(
+                buf["scratch"].data_ptr(), buf["n_cta"], a.numel, a.flat.data_ptr(), opt.exp_avg.data_ptr(),
+                opt.exp_avg_sq.data_ptr(), C.byref(o), None, slot.data_ptr(), sp), "fused_update")
+        else:
+            self.comm.allreduce_update(buf["scratch"], buf["n_cta"], a, opt, o, slot)
+        _native.count_launch(3)
+        self.n_steps += 1
+        return slot
+
+    def train_step_gather(self, feats: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+        """K11 gather from a device-resident dataset (feats [N,T,I], labels [N] or [N,1]) then train_step."""
+        B = idx.numel()
+        T, I = feats.shape[1], feats.shape[2]
+        buf = self._get(B, T)
+        if buf["x"] is None:
+            buf["x"] = torch.empty(B, T, I, dtype=torch.float32, device=self.device)
+            buf["y"] = torch.empty(B, dtype=torch.int64, device=self.device)
+        _native.check(self.lib.b200rnn_gather_batch(feats.data_ptr(), labels.data_ptr(), idx.data_ptr(), B, T * I,
+                                                    buf["x"].data_ptr(), buf["y"].data_ptr(),
+                                                    _native.stream_ptr(self.device)), "gather_batch")
+        _native.count_launch()
+        return self.train_step(buf["x"], buf["y"])
+
+    @torch.no_grad()
+    def evaluate(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """Forward + head only. Returns device view [2] = (loss sum, correct count)."""
+        B, T, _ = x.shape
+        buf = self._get(B, T)
+        d = buf["desc"]
+        y = y.reshape(-1)
+        sp = _native.stream_ptr(self.device)
+        a, m = self.arena, self.model
+        H, L = m.hidden_dim, m.layer_dim
+        _native.check(self.lib.b200rnn_lstm_fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 0, sp), "lstm_fwd")
+        h_last = buf["stash"][((L - 1) * T + (T - 1)) * B * H:][:B * H]
+        _native.check(self.lib.b200rnn_head_fwd(h_last.data_ptr(), H, m.fc.weight.data_ptr(), m.fc.bias.data_ptr(),
+                                                y.data_ptr(), B, H, m.output_dim, None, self.eval_metrics.data_ptr(), sp), "head_fwd")
+        _native.count_launch(3)
+        return self.eval_metrics[:2]

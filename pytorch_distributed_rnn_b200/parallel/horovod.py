@@ -1,0 +1,162 @@
+"""Horovod-style synchronous data parallelism: the all-reduce lives in the optimizer.
+
+API surface the reference uses from ``horovod.torch`` (src/motion/trainer/horovod.py:17-42,
+src/example/example_horovod.py:42-53,80-83): ``init``, ``rank``, ``size``, ``local_rank``,
+``broadcast_parameters(state_dict, root_rank)``, ``DistributedOptimizer(optimizer,
+named_parameters)``, plus ``allreduce`` / ``broadcast_optimizer_state`` for completeness.
+
+Horovod's C++ core negotiates tensor readiness by name through a rank-0 coordinator and
+packs ready tensors into a fusion buffer each cycle.  Training graphs here are static, so
+no negotiation is needed: the fusion plan is fixed at construction (all named gradients,
+one buffer in parameter order), gradient hooks fire the fused all-reduce (op = Average) as
+soon as the last gradient of the step is produced, and ``step()`` is the synchronisation
+point — same semantics, zero coordinator round-trips.  The model is NOT wrapped, so
+``state_dict()`` keys stay un-prefixed (contrast :mod:`.ddp`).
+"""
+from __future__ import annotations
+
+from typing import Iterable, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+from torch._utils import _flatten_dense_tensors, _unflatten_dense_tensors
+
+from . import process_group as pg
+from .comm import TorchDistComm, make_comm
+
+_comm = None
+
+
+def init(comm=None):
+    global _comm
+    pg.init_distributed()
+    _comm = comm if comm is not None else make_comm()
+    return _comm
+
+
+def _c():
+    if _comm is None:
+        init()
+    return _comm
+
+
+def rank() -> int:
+    return _c().rank
+
+
+def size() -> int:
+    return _c().world
+
+
+def local_rank() -> int:
+    return pg.rank_info().local_rank
+
+
+def allreduce(tensor: torch.Tensor, average: bool = True) -> torch.Tensor:
+    out = tensor.clone()
+    _c().allreduce_flat(out.view(-1), average=average)
+    return out
+
+
+def broadcast_parameters(params, root_rank: int = 0) -> None:
+    """Broadcast a ``state_dict()`` or an iterable of ``(name, tensor)`` from ``root_rank`` in place.
+
+    One fused message (S10 in SURVEY §2.5 issues one broadcast per entry; here entries of the
+    same dtype are packed)."""
+    if isinstance(params, dict):
+        items = sorted(params.items())
+    else:
+        items = sorted(list(params))
+    tensors = [t for _, t in items if isinstance(t, torch.Tensor)]
+    if not tensors or size() == 1:
+        return
+    by_dtype = {}
+    for t in tensors:
+        by_dtype.setdefault((t.dtype, t.device), []).append(t)
+    for group in by_dtype.values():
+        flat = _flatten_dense_tensors([t.detach() for t in group])
+        _c().broadcast_flat(flat, root=root_rank)
+        for t, src in zip(group, _unflatten_dense_tensors(flat, group)):
+            t.detach().copy_(src)
+
+
+def broadcast_optimizer_state(optimizer: torch.optim.Optimizer, root_rank: int = 0) -> None:
+    tensors = []
+    for st in optimizer.state.values():
+        for k in sorted(st):
+            if isinstance(st[k], torch.Tensor):
+                tensors.append((k, st[k]))
+    for name in ("exp_avg", "exp_avg_sq"):  # flat optimizers keep state outside .state
+        t = getattr(optimizer, name, None)
+        if isinstance(t, torch.Tensor):
+            tensors.append((name, t))
+    broadcast_parameters([(f"{i}.{k}", t) for i, (k, t) in enumerate(tensors)], root_rank)
+
+
+class DistributedOptimizer:
+    """Wraps any ``torch.optim.Optimizer``; averages gradients across ranks before ``step()``."""
+
+    def __init__(self, optimizer: torch.optim.Optimizer, named_parameters: Optional[Iterable[Tuple[str, torch.Tensor]]] = None):
+        self._opt = optimizer
+        self._comm = _c()
+        if named_parameters is not None:
+            named = list(named_parameters)
+        else:
+            named = [(f"p{i}", p) for g in optimizer.param_groups for i, p in enumerate(g["params"])]
+        names = [n for n, _ in named]
+        if len(set(names)) != len(names):
+            raise ValueError("named_parameters must have unique names")
+        self._params = [p for _, p in named if p.requires_grad]
+        self._ready = 0
+        self._work = None
+        self._flat = None
+        self._synced = True
+        if self._comm.world > 1:
+            for p in self._params:
+                p.register_post_accumulate_grad_hook(self._hook)
+
+    # delegate everything else (param_groups, state_dict, zero_grad, ...) to the wrapped optimizer
+    def __getattr__(self, name):
+        return getattr(self._opt, name)
+
+    def _hook(self, p):
+        self._ready += 1
+        if self._ready == len(self._params):
+            self._launch()
+
+    def _launch(self):
+        grads = [p.grad for p in self._params if p.grad is not None]
+        arena = getattr(self._opt, "arena", None)
+        if arena is not None and all(g.data_ptr() == arena.grad[o:o + 1].data_ptr()
+                                     for g, (o, k, s) in zip(grads, arena.index.values())) and len(grads) == len(arena.index):
+            self._flat, self._grads = arena.grad[:arena.numel], None  # already one fusion buffer
+        else:
+            self._flat, self._grads = _flatten_dense_tensors(grads), grads
+        if isinstance(self._comm, TorchDistComm):
+            self._work = dist.all_reduce(self._flat, async_op=True)
+        else:
+            self._comm.allreduce_flat(self._flat, average=False)
+            self._work = None
+        self._synced = False
+
+    def synchronize(self):
+        if self._comm.world == 1:
+            return
+        if self._synced and self._ready < len(self._params):
+            self._launch()  # some gradients never fired (unused parameters / manual grads)
+        if not self._synced:
+            if self._work is not None:
+                self._work.wait()
+            self._flat.div_(self._comm.world)
+            if self._grads is not None:
+                for g, src in zip(self._grads, _unflatten_dense_tensors(self._flat, self._grads)):
+                    g.copy_(src)
+            self._synced = True
+        self._ready = 0
+
+    def step(self, closure=None):
+        self.synchronize()
+        return self._opt.step(closure)
+
+    def zero_grad(self, *a, **kw):
+        return self._opt.zero_grad(*a, **kw)

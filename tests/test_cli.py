@@ -1,0 +1,35 @@
+"""Flag system parity with src/motion/main.py:17-36 and param_server/__init__.py:13-35."""
+from pathlib import Path
+
+import pytest
+
+from pytorch_distributed_rnn_b200 import cli
+
+
+def test_defaults_match_reference():
+    a = cli.build_parser().parse_args(["local"])
+    assert (a.stacked_layer, a.hidden_units, a.epochs, a.batch_size) == (2, 32, 100, 1440)
+    assert (a.validation_fraction, a.learning_rate, a.dropout, a.log, a.num_threads) == (0.1, 0.0025, 0.1, "INFO", 4)
+    assert a.seed is None and a.no_validation is False and a.output_path is None
+    assert isinstance(a.checkpoint_directory, Path) and isinstance(a.dataset_path, Path)
+
+
+def test_subcommands_and_ps_flags():
+    p = cli.build_parser()
+    for name in ("local", "distributed", "horovod"):
+        assert callable(p.parse_args(["--epochs", "1", "--seed", "123456789", "--no-validation", name]).func)
+    a = p.parse_args(["parameter-server", "--world-size", "3", "--rank", "1"])
+    assert (a.world_size, a.rank, a.master_address, a.master_port) == (3, 1, "localhost", "29500")
+    with pytest.raises(SystemExit):
+        p.parse_args([])  # sub-command is required
+    with pytest.raises(SystemExit):
+        p.parse_args(["parameter-server"])  # --world-size / --rank are required
+
+
+def test_local_run_resume_and_periodic_checkpoint(tiny_dataset_dir, tmp_path):
+    common = ["--dataset-path", str(tiny_dataset_dir), "--batch-size", "96", "--seed", "7", "--device", "cpu",
+              "--checkpoint-directory", str(tmp_path / "ck"), "--history-path", str(tmp_path / "h.json")]
+    t = cli.main([*common, "--epochs", "1", "--save-every", "1", "local"])
+    assert (tmp_path / "ck" / "best-model.pt").exists() and (tmp_path / "ck" / "checkpoint-epoch-1.pt").exists()
+    t2 = cli.main([*common, "--epochs", "2", "--resume", str(tmp_path / "ck" / "checkpoint-epoch-1.pt"), "local"])
+    assert t2.start_epoch == 1 and t2.optimizer.step_count == 2 * t.optimizer.step_count
