@@ -1,0 +1,330 @@
+#!/usr/bin/env python
+"""Headline benchmark: motion-LSTM data-parallel training throughput (samples/s).
+
+Config (BASELINE.json / BASELINE.md): the reference's motion classifier — LSTM 9->32, 2 layers,
+T=128, Linear 32->6, CrossEntropy, Adam lr 0.0025, fp32 — at GLOBAL batch 1440 (per-rank batch
+1440 // N, the reference's rule, src/motion/trainer/distributed.py:48-49 => strong scaling), on
+synthetic data of the reference's shape (6 912 x [128, 9]) with random-init weights.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl own|reference]
+
+N > 1 is launched by the driver under torchrun (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* env).
+Rank 0 prints ONE JSON line.  Two measurements per run:
+
+* ``value``   — device time: every step bracketed by CUDA events on the launching stream, a
+  256 MiB L2 flush between steps (outside the brackets), summed over K steps, max over ranks.
+  The step is K11 gather from the device-resident dataset -> fused forward -> fused
+  head/CE/backward -> fused grad-reduce/all-reduce/Adam: 4 launches of this repo's kernels.
+* ``e2e``     — wall clock through the public API a user calls
+  (``FusedTrainEngine.train_step_host``): every step copies that step's inputs from pinned
+  host memory to the GPU and reads the step's loss back to the host.
+
+``--impl reference`` runs the UNMODIFIED reference (installed at baseline/_ref) through its own
+Trainer loop on the same GPUs (stock torch cuDNN LSTM + NCCL DistributedDataParallel); see
+baseline/ref_adapter.py.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+GLOBAL_BATCH, SEQ_LEN, FEATURES, HIDDEN, LAYERS, CLASSES, TRAIN_SIZE = 1440, 128, 9, 32, 2, 6, 6912
+LR, SEED = 0.0025, 123456789
+# best published number of the reference at batch 1440: 6912 samples / 3.595 s on its unnamed fast
+# host (results_baseline_1.json results[0])
+BASELINE_SAMPLES_PER_S = 6912 / 3.595
+METRIC = "motion_lstm_ddp_train_samples_per_sec"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons, sampled while the benchmark runs (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.rows = []  # (t, sm, max, {reason: bool})
+        self.proc = None
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm, mx = float(f[1]), float(f[2])
+            except ValueError:
+                continue
+            names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+            self.rows.append((time.time(), sm, mx, {n: f[5 + i].lower().startswith("active") for i, n in enumerate(names)}))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self, windows):
+        def inside(t):
+            return any(a - 0.05 <= t <= b + 0.05 for a, b in windows)
+        rows = [r for r in self.rows if inside(r[0])]
+        scope = "timed_regions"
+        if not rows:
+            rows, scope = self.rows, "whole_benchmark_process(timed region shorter than the 100 ms sampling period)"
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "window": "nvidia-smi unavailable"}
+        reasons = sorted({n for r in rows for n, on in r[3].items() if on})
+        return {"sm_mhz": statistics.median(r[1] for r in rows), "sm_max_mhz": max(r[2] for r in rows),
+                "reasons": reasons, "samples": len(rows), "window": scope}
+
+
+def dist_setup(n_gpus: int):
+    import torch
+    if n_gpus > 1:
+        from pytorch_distributed_rnn_b200.parallel import process_group as pg
+        info = pg.init_distributed()
+        assert info.world_size == n_gpus, f"--gpus {n_gpus} but WORLD_SIZE={info.world_size} (launch under torchrun)"
+        return info.rank, info.world_size, info.device
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+    return 0, 1, dev
+
+
+def max_over_ranks(x: float, world: int, dev) -> float:
+    import torch
+    if world == 1:
+        return x
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def barrier_sync(world: int, dev):
+    import torch
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+
+
+def run_own(args):
+    import torch
+    from pytorch_distributed_rnn_b200 import MotionModel, ParamArena, _native
+    from pytorch_distributed_rnn_b200.data import synthetic
+    from pytorch_distributed_rnn_b200.data.sampler import epoch_indices
+    from pytorch_distributed_rnn_b200.ops.engine import FusedTrainEngine
+
+    rank, world, dev = dist_setup(args.gpus)
+    lib = _native.lib()
+    torch.manual_seed(SEED)
+    model = MotionModel(FEATURES, HIDDEN, LAYERS, CLASSES).to(dev)
+    comm, arena, comm_kind = None, None, "none"
+    if world > 1:
+        from pytorch_distributed_rnn_b200.parallel.comm import make_comm
+        comm = make_comm()
+        comm_kind = comm.kind
+        arena = comm.make_arena(model) if hasattr(comm, "make_arena") else ParamArena(model)
+        comm.broadcast_flat(arena.flat[:arena.numel], root=0)
+    engine = FusedTrainEngine(model, lr=LR, arena=arena, comm=comm)
+    per_rank = GLOBAL_BATCH // world
+    K, W = args.steps, args.warmup
+
+    # synthetic dataset of the reference's shape, device-resident (value) and pinned on the host (e2e)
+    x_all, y_all = synthetic.make_split(TRAIN_SIZE, seed=0)
+    feats, labels = x_all.to(dev), y_all.to(dev)
+    full = TRAIN_SIZE // GLOBAL_BATCH  # 4 full global batches per epoch (the 5th, partial one is skipped)
+
+    def step_indices(s):
+        e, j = divmod(s, full)
+        return epoch_indices(TRAIN_SIZE, world, rank, e)[j * per_rank:(j + 1) * per_rank]
+
+    idx_dev = [step_indices(s).to(dev) for s in range(W + K)]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    sp = _native.stream_ptr(dev)
+
+    sampler = ClockSampler(dev.index or 0) if rank == 0 else None
+    if sampler:
+        sampler.start()
+
+    # ---------------- device-timed value ----------------
+    for s in range(W):
+        engine.train_step_gather(feats, labels, idx_dev[s])
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    barrier_sync(world, dev)
+    launches0 = _native.launches()
+    t_a = time.time()
+    for s in range(K):
+        lib.b200rnn_l2_flush(flush.data_ptr(), flush.numel(), sp)
+        ev[s][0].record()
+        engine.train_step_gather(feats, labels, idx_dev[W + s])
+        ev[s][1].record()
+    barrier_sync(world, dev)
+    t_b = time.time()
+    launches = _native.launches() - launches0
+    dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+    dev_ms = max_over_ranks(dev_ms, world, dev)
+    last = engine.metrics[(engine.n_steps - 1) % engine.METRIC_RING].cpu()
+
+    # ---------------- end-to-end through the public API ----------------
+    ring = 8
+    host = []
+    for s in range(ring):
+        i = step_indices(s)
+        host.append((x_all[i].contiguous().pin_memory(), y_all[i].contiguous().view(-1).pin_memory()))
+    for s in range(max(W, 3)):
+        engine.train_step_host(*host[s % ring])
+    barrier_sync(world, dev)
+    t_c = time.time()
+    t0 = time.perf_counter()
+    for s in range(K):
+        loss, correct = engine.train_step_host(*host[s % ring])
+    barrier_sync(world, dev)
+    e2e_s = time.perf_counter() - t0
+    t_d = time.time()
+    e2e_s = max_over_ranks(e2e_s, world, dev)
+    h2d = world * (host[0][0].numel() * 4 + host[0][1].numel() * 8)
+    d2h = world * 8
+
+    clocks = None
+    if sampler:
+        sampler.stop()
+        clocks = sampler.summary([(t_a, t_b), (t_c, t_d)])
+
+    if rank == 0:
+        value = GLOBAL_BATCH * K / (dev_ms / 1e3)
+        out = {
+            "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": value / BASELINE_SAMPLES_PER_S, "dtype": "fp32", "data": "synthetic",
+            "impl": "own",
+            "config": {"model": "motion LSTM 9->32 x2 layers, T=128, Linear 32->6, CE, Adam lr 0.0025",
+                       "global_batch": GLOBAL_BATCH, "seq_len": SEQ_LEN, "parallelism": f"dp{world}",
+                       "per_rank_batch": per_rank, "comm": comm_kind,
+                       "l2": "256 MiB L2 flush between timed steps, outside the CUDA-event brackets",
+                       "timing": "per-step CUDA events on the launching stream, summed, max over ranks",
+                       "baseline_number": "1922.7 samples/s = 6912/3.595 s, reference local bs1440 on its fast host"},
+            "e2e": {"value": GLOBAL_BATCH * K / e2e_s, "unit": "samples/s", "ms_per_step": 1e3 * e2e_s / K,
+                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "api": "FusedTrainEngine.train_step_host(x_pinned, y_pinned) -> (loss, correct)",
+                    "inputs": f"{ring} pre-collated pinned host batches, one H2D copy + one D2H loss read per step"},
+            "gpu_launches": launches,
+            "launches_per_step": launches / K,
+            "clocks": clocks,
+            "final_loss": float(last[0]) / per_rank,
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        barrier_sync(world, dev)
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    try:
+        from baseline import ref_adapter
+    except Exception as e:  # noqa: BLE001
+        print(json.dumps({"impl": "reference", "unavailable": f"adapter import failed: {type(e).__name__}: {e}"}), flush=True)
+        return
+    why = ref_adapter.unavailable_reason()
+    if why:
+        rank = int(os.environ.get("RANK", "0"))
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
+        return
+    rank, world, dev = dist_setup_reference(args.gpus)
+    sampler = ClockSampler(dev.index or 0) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    res = ref_adapter.run(args.gpus, args.steps, args.warmup, rank, world, dev,
+                          dict(global_batch=GLOBAL_BATCH, seq_len=SEQ_LEN, features=FEATURES, hidden=HIDDEN,
+                               layers=LAYERS, classes=CLASSES, lr=LR, seed=SEED))
+    clocks = None
+    if sampler:
+        sampler.stop()
+        clocks = sampler.summary([res["window"]])
+    dev_s = max_over_ranks(res["device_s"], world, dev)
+    wall_s = max_over_ranks(res["wall_s"], world, dev)
+    if rank == 0:
+        K = args.steps
+        value = GLOBAL_BATCH * K / dev_s
+        out = {
+            "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
+            "ms_per_step": 1e3 * dev_s / K, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": value / BASELINE_SAMPLES_PER_S, "dtype": "fp32", "data": "synthetic", "impl": "reference",
+            "config": {"model": "reference MotionModel (nn.LSTM 9->32 x2, T=128, Linear 32->6), CE, Adam lr 0.0025",
+                       "global_batch": GLOBAL_BATCH, "seq_len": SEQ_LEN, "parallelism": f"dp{world}",
+                       "per_rank_batch": GLOBAL_BATCH // world,
+                       "path": res["path"],
+                       "timing": "CUDA events around the reference's own _train_step loop (K steps), max over ranks"},
+            "e2e": {"value": GLOBAL_BATCH * K / wall_s, "unit": "samples/s", "ms_per_step": 1e3 * wall_s / K,
+                    "h2d_bytes_per_step": res["h2d_bytes_per_step"], "d2h_bytes_per_step": res["d2h_bytes_per_step"]},
+            "gpu_launches": None,
+            "clocks": clocks,
+            "final_loss": res.get("final_loss"),
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def dist_setup_reference(n_gpus: int):
+    """Same rendezvous as the own arm, but with torch only (none of this repo's engine on the reference path)."""
+    import torch
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if n_gpus > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+        assert dist.get_world_size() == n_gpus
+        return dist.get_rank(), dist.get_world_size(), dev
+    return 0, 1, dev
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3  # timing rule: at least 3 warm-up steps
+    import torch
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device visible"}), flush=True)
+        return
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_own(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -49,6 +49,7 @@ class FusedTrainEngine:
         self.metrics = torch.zeros(self.METRIC_RING, 2, dtype=torch.float32, device=self.device)
         self.eval_metrics = torch.zeros(256, dtype=torch.float32, device=self.device)
         self.n_steps = 0
+        self._host_metrics = None
         d = self._desc(1, 1)
         if not self.lib.b200rnn_rnn_small_supported(C.byref(d)):
             raise NotImplementedError(
@@ -126,6 +127,24 @@ class FusedTrainEngine:
                                                     _native.stream_ptr(self.device)), "gather_batch")
         _native.count_launch()
         return self.train_step(buf["x"], buf["y"])
+
+    def train_step_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> Tuple[float, int]:
+        """End-to-end step from host memory: H2D copy of the batch (pass pinned tensors for an async
+        DMA), the 3-launch training step, and a D2H read of this step's result.
+        Returns (mean cross-entropy loss of the batch, correct count)."""
+        B, T, I = x_host.shape
+        buf = self._get(B, T)
+        if buf["x"] is None:
+            buf["x"] = torch.empty(B, T, I, dtype=torch.float32, device=self.device)
+            buf["y"] = torch.empty(B, dtype=torch.int64, device=self.device)
+        if self._host_metrics is None:
+            self._host_metrics = torch.zeros(2, dtype=torch.float32).pin_memory()
+        buf["x"].copy_(x_host, non_blocking=True)
+        buf["y"].copy_(y_host.reshape(-1), non_blocking=True)
+        m = self.train_step(buf["x"], buf["y"])
+        self._host_metrics.copy_(m, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return float(self._host_metrics[0]) / B, int(round(float(self._host_metrics[1])))
 
     @torch.no_grad()
     def evaluate(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:

@@ -1,0 +1,145 @@
+"""Numerics of the hand-written sm_100a kernels against plain PyTorch fp32 references."""
+import copy
+import ctypes as C
+
+import pytest
+import torch
+from torch import nn
+
+from pytorch_distributed_rnn_b200 import FusedAdam, FusedLSTM, MotionModel, ParamArena, _native
+from pytorch_distributed_rnn_b200.ops.engine import FusedTrainEngine
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _stock_lstm(m: FusedLSTM) -> nn.LSTM:
+    s = nn.LSTM(m.input_size, m.hidden_size, m.num_layers, batch_first=True)
+    s.load_state_dict({k: v.detach().cpu() for k, v in m.state_dict().items()})
+    return s
+
+
+def test_native_library_is_loaded():
+    assert _native.available(), "libb200rnn.so must be loadable on a GPU box"
+    assert _native.lib().b200rnn_version() >= 100
+
+
+@pytest.mark.parametrize("B,T,I,L", [(5, 7, 9, 1), (37, 16, 9, 2), (64, 128, 9, 2), (1440, 128, 9, 2), (33, 12, 20, 3), (300, 5, 32, 2)])
+def test_lstm_forward_matches_torch(B, T, I, L):
+    torch.manual_seed(B + T)
+    m = FusedLSTM(I, 32, L, batch_first=True).to(DEV)
+    ref = _stock_lstm(m)
+    x = torch.randn(B, T, I)
+    out, (h, c) = m(x.to(DEV))
+    with torch.no_grad():
+        ro, (rh, rc) = ref(x)
+    assert out.shape == (B, T, 32) and h.shape == (L, B, 32)
+    assert torch.allclose(out.cpu(), ro, atol=2e-5, rtol=1e-4), float((out.cpu() - ro).abs().max())
+    assert torch.allclose(h.cpu(), rh, atol=2e-5, rtol=1e-4)
+    assert torch.allclose(c.cpu(), rc, atol=2e-5, rtol=1e-4)
+
+
+@pytest.mark.parametrize("B,T,I,L", [(6, 5, 9, 1), (37, 16, 9, 2), (130, 33, 9, 2), (19, 9, 24, 3)])
+def test_lstm_backward_matches_torch(B, T, I, L):
+    torch.manual_seed(7 * B + L)
+    m = FusedLSTM(I, 32, L, batch_first=True).to(DEV)
+    ref = _stock_lstm(m)
+    x = torch.randn(B, T, I)
+    wo, wh, wc = torch.randn(B, T, 32), torch.randn(L, B, 32), torch.randn(L, B, 32)
+    out, (h, c) = m(x.to(DEV))
+    ((out * wo.to(DEV)).sum() + (h * wh.to(DEV)).sum() + (c * wc.to(DEV)).sum()).backward()
+    ro, (rh, rc) = ref(x)
+    ((ro * wo).sum() + (rh * wh).sum() + (rc * wc).sum()).backward()
+    for (n, p), q in zip(m.named_parameters(), ref.parameters()):
+        err = float((p.grad.cpu() - q.grad).abs().max())
+        scale = float(q.grad.abs().max()) + 1e-6
+        assert err <= 2e-4 * scale + 2e-5, (n, err, scale)
+
+
+def _ref_train(model_cpu, xs, ys, lr, steps):
+    opt = torch.optim.Adam(model_cpu.parameters(), lr=lr)
+    metrics = []
+    for s in range(steps):
+        opt.zero_grad()
+        out = model_cpu(xs[s])
+        loss = nn.functional.cross_entropy(out, ys[s])
+        loss.backward()
+        opt.step()
+        metrics.append((loss.item(), int((out.argmax(1) == ys[s]).sum())))
+    return metrics
+
+
+@pytest.mark.parametrize("B,T,L", [(96, 32, 2), (1440, 128, 2), (50, 10, 1)])
+def test_engine_train_steps_match_torch_adam(B, T, L):
+    torch.manual_seed(B)
+    steps, lr = 3, 0.0025
+    model = MotionModel(9, 32, L, 6)
+    ref = copy.deepcopy(model)
+    xs = [torch.randn(B, T, 9) for _ in range(steps)]
+    ys = [torch.randint(0, 6, (B,)) for _ in range(steps)]
+    want = _ref_train(ref, xs, ys, lr, steps)
+    model = model.to(DEV)
+    eng = FusedTrainEngine(model, lr=lr)
+    got = []
+    for s in range(steps):
+        m = eng.train_step(xs[s].to(DEV), ys[s].to(DEV).view(-1, 1)).cpu()
+        got.append((float(m[0]) / B, int(round(float(m[1])))))
+    for (gl, gc), (wl, wc) in zip(got, want):
+        assert abs(gl - wl) < 2e-5, (got, want)
+        assert abs(gc - wc) <= max(1, B // 500), (got, want)  # ties in argmax may flip on rounding
+    for (n, p), q in zip(model.named_parameters(), ref.parameters()):
+        assert torch.allclose(p.detach().cpu(), q.detach(), atol=3e-5), (n, float((p.detach().cpu() - q).abs().max()))
+    # Adam state is exported in the stock format
+    sd = eng.optimizer.state_dict()
+    assert float(sd["state"][0]["step"]) == steps and sd["state"][0]["exp_avg"].shape == (128, 9)
+
+
+def test_engine_evaluate_and_head():
+    torch.manual_seed(0)
+    model = MotionModel(9, 32, 2, 6)
+    x, y = torch.randn(367, 128, 9), torch.randint(0, 6, (367, 1))
+    with torch.no_grad():
+        out = model(x)
+        want_loss = nn.functional.cross_entropy(out, y.view(-1), reduction="sum").item()
+        want_corr = int((out.argmax(1) == y.view(-1)).sum())
+    eng = FusedTrainEngine(model.to(DEV))
+    m = eng.evaluate(x.to(DEV), y.to(DEV)).cpu()
+    assert abs(float(m[0]) - want_loss) < 2e-3 and abs(int(round(float(m[1]))) - want_corr) <= 1
+
+
+def test_gather_kernel():
+    lib = _native.lib()
+    feats = torch.randn(500, 128, 9, device=DEV)
+    labels = torch.randint(0, 6, (500, 1), device=DEV)
+    idx = torch.randperm(500, device=DEV)[:77]
+    xo = torch.empty(77, 128, 9, device=DEV)
+    yo = torch.empty(77, dtype=torch.int64, device=DEV)
+    _native.check(lib.b200rnn_gather_batch(feats.data_ptr(), labels.data_ptr(), idx.data_ptr(), 77, 128 * 9,
+                                           xo.data_ptr(), yo.data_ptr(), _native.stream_ptr()))
+    assert torch.equal(xo, feats[idx]) and torch.equal(yo, labels[idx].view(-1))
+
+
+def test_fused_adam_kernel_matches_torch():
+    torch.manual_seed(3)
+    a = nn.Linear(37, 11).to(DEV)
+    b = copy.deepcopy(a)
+    fa = FusedAdam(ParamArena(a), lr=0.01)
+    sa = torch.optim.Adam(b.parameters(), lr=0.01)
+    for _ in range(4):
+        x = torch.randn(9, 37, device=DEV)
+        for mod, opt in ((a, fa), (b, sa)):
+            opt.zero_grad()
+            mod(x).pow(2).sum().backward()
+            opt.step()
+    for p, q in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(p, q, atol=1e-6)
+
+
+def test_unsupported_shape_falls_back_to_composite_and_is_correct():
+    torch.manual_seed(1)
+    m = FusedLSTM(9, 48, 2, batch_first=True).to(DEV)  # H=48: outside the fused family
+    ref = nn.LSTM(9, 48, 2, batch_first=True)
+    ref.load_state_dict({k: v.detach().cpu() for k, v in m.state_dict().items()})
+    x = torch.randn(4, 6, 9)
+    out, _ = m(x.to(DEV))
+    assert torch.allclose(out.detach().cpu(), ref(x)[0], atol=1e-4)

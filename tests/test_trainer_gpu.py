@@ -1,0 +1,50 @@
+"""End-to-end trainer on the GPU: same log lines / numbers as the CPU torch path, checkpoints load into stock torch."""
+import logging
+import re
+
+import pytest
+import torch
+from torch import nn
+
+from pytorch_distributed_rnn_b200 import MotionDataset, MotionModel
+from pytorch_distributed_rnn_b200.data import synthetic
+from pytorch_distributed_rnn_b200.trainer import Trainer
+
+pytestmark = pytest.mark.gpu
+STEP_RE = re.compile(r"Train Batch: (\d+)/(\d+) .*Loss: ([\d.]+)\tAcc: (\d+)/(\d+)")
+
+
+def _run(device, caplog, tmp_path, deferred=False):
+    (xtr, ytr), (xv, yv), (xte, yte) = synthetic.make_datasets(seed=0, train=960, valid=50, test=60)
+    torch.manual_seed(123456789)
+    model = MotionModel(9, 32, 2, 6)
+    t = Trainer(model, MotionDataset(xtr, ytr), 480, 0.0025, validation_set=MotionDataset(xv, yv),
+                test_set=MotionDataset(xte, yte), checkpoint_dir=tmp_path / f"ck_{device}", device=device,
+                deferred_logging=deferred)
+    caplog.clear()
+    with caplog.at_level(logging.INFO):
+        _, th, vh = t.train(2)
+    steps = [(int(m[1]), float(m[3]), int(m[4])) for m in STEP_RE.finditer(caplog.text)]
+    return t, th, vh, steps, caplog.text
+
+
+def test_gpu_trainer_matches_cpu_trainer(caplog, tmp_path):
+    tc, thc, vhc, sc, _ = _run("cpu", caplog, tmp_path)
+    tg, thg, vhg, sg, text = _run("cuda", caplog, tmp_path)
+    assert tg.engine is not None, "the fused engine must be the path that runs on CUDA"
+    assert len(sc) == len(sg) == 4
+    for (b1, l1, c1), (b2, l2, c2) in zip(sc, sg):
+        assert b1 == b2 and abs(l1 - l2) < 2e-5 and abs(c1 - c2) <= 1
+    assert all(abs(a - b) < 1e-6 for a, b in zip(thc, thg)) and all(abs(a - b) < 1e-4 for a, b in zip(vhc, vhg))
+    assert re.search(r"0: Memory Usage: \d+\.\d+, Training Duration: \d+\.\d+", text)
+    assert "Test Evaluation:" in text
+    ck = torch.load(tmp_path / "ck_cuda" / "best-model.pt", weights_only=False)
+    ref = nn.LSTM(9, 32, 2, batch_first=True)
+    ref.load_state_dict({k[5:]: v for k, v in ck["model_state"].items() if k.startswith("lstm.")})
+    assert ck["optimizer_state"]["state"][0]["exp_avg"].shape == (128, 9)
+
+
+def test_deferred_logging_same_lines(caplog, tmp_path):
+    _, _, _, s1, _ = _run("cuda", caplog, tmp_path)
+    _, _, _, s2, _ = _run("cuda", caplog, tmp_path, deferred=True)
+    assert s1 == s2
