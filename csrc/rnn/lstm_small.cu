@@ -675,3 +675,94 @@ extern "C" int b200rnn_lstm_bwd(const b200rnn_model_desc* d, const float* params
   set_error("lstm_bwd: internal tiling error (ng=%d)", ng);
   return B200RNN_EINVAL;
 }
+
+// ---------------------------------------------------------------------------
+// Allocation-free backward (see include/b200rnn.h: b200rnn_lstm_bwd_static).
+//
+// Some hosts of this library cannot give the backward pass a scratch buffer: a plain C/C++
+// program that links the C ABI without torch's caching allocator, a service that handed the
+// whole GPU to its own memory pool at start-up (so cudaMalloc has nothing left and fails),
+// or a latency-sensitive loop that must not call cudaMalloc/cudaFree because both serialise
+// the device.  For them the per-CTA gradient rows and the inter-layer dx buffers live in the
+// fixed array below instead of caller memory.  Cost: every GPU that loads the library keeps
+// B200RNN_STATIC_SCRATCH_FLOATS * 4 bytes (16 MiB) reserved until the process exits.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) float g_bwd_static_scratch[B200RNN_STATIC_SCRATCH_FLOATS];
+
+namespace b200rnn {
+namespace {
+
+constexpr int kMaxDevices = 64;
+float* g_static_ptr[kMaxDevices] = {nullptr};  // device address of g_bwd_static_scratch, per device
+
+// In host code `g_bwd_static_scratch` is only a handle for the runtime, not a device address;
+// the real address differs per device and has to be asked for with that device current.
+int static_scratch_for_current_device(float** out) {
+  int dev = -1;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kMaxDevices, B200RNN_EINVAL, "lstm_bwd_static: device index %d out of range", dev);
+  if (g_static_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    B200_CHECK_CUDA(cudaGetSymbolAddress((void**)&p, g_bwd_static_scratch));
+    B200_REQUIRE(p != nullptr, B200RNN_ECUDA, "lstm_bwd_static: cudaGetSymbolAddress returned NULL");
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return B200RNN_OK;
+}
+
+}  // namespace
+}  // namespace b200rnn
+
+extern "C" int b200rnn_lstm_bwd_static(const b200rnn_model_desc* d, const float* params, const float* x,
+                                       const float* stash, const int64_t* labels, float loss_scale,
+                                       const float* d_out, const float* d_hn, const float* d_cn,
+                                       float* grad_out, void* stream) {
+  B200_REQUIRE(d && params && x && stash && grad_out, B200RNN_EINVAL, "lstm_bwd_static: null argument");
+  B200_REQUIRE(small_supported(d), B200RNN_EUNSUPPORTED,
+               "lstm_bwd_static: shape (cell=%d I=%d H=%d L=%d C=%d) not covered by the small-hidden family",
+               d->cell, d->input_size, d->hidden_size, d->num_layers, d->num_classes);
+  const int64_t need = b200rnn_rnn_bwd_scratch_floats(d);
+  B200_REQUIRE(need <= (int64_t)B200RNN_STATIC_SCRATCH_FLOATS, B200RNN_ETOOBIG,
+               "lstm_bwd_static: this shape needs %lld scratch floats but the built-in scratch holds %lld "
+               "(B200RNN_STATIC_SCRATCH_FLOATS); use b200rnn_lstm_bwd with a caller-provided buffer",
+               (long long)need, (long long)B200RNN_STATIC_SCRATCH_FLOATS);
+  float* scratch = nullptr;
+  int rc = static_scratch_for_current_device(&scratch);
+  if (rc != B200RNN_OK) return rc;
+
+  // Same launch as b200rnn_lstm_bwd, pointed at the built-in scratch.  Nothing in it has to start
+  // at zero: every gradient-row slot and every dx element is written by the kernel before it is read.
+  BwdArgs a;
+  a.x = x; a.params = params;
+  const int64_t lsz = (int64_t)d->num_layers * d->seq_len * d->batch * d->hidden_size;
+  a.h_seq = stash; a.c_seq = stash + lsz; a.g_seq = stash + 2 * lsz;
+  a.labels = labels; a.d_out = d_out; a.d_hn = d_hn; a.d_cn = d_cn;
+  for (int l = 0; l < B200RNN_MAX_LAYERS; ++l) {
+    a.off_wih[l] = d->off_wih[l]; a.off_whh[l] = d->off_whh[l];
+    a.off_bih[l] = d->off_bih[l]; a.off_bhh[l] = d->off_bhh[l];
+  }
+  a.off_fcw = d->off_fcw; a.off_fcb = d->off_fcb; a.n_params = d->n_params;
+  a.row_floats = d->n_params + 2;
+  a.loss_scale = loss_scale;
+  a.I = d->input_size; a.T = d->seq_len; a.B = d->batch; a.L = d->num_layers;
+  a.C = d->num_classes;
+  a.BT = choose_bt(d->batch);
+  const int n_cta = (a.B + a.BT - 1) / a.BT;
+  a.rows = scratch;
+  a.dxbuf = scratch + (int64_t)n_cta * a.row_floats;
+  const int ng = (a.BT + kKQ - 1) / kKQ;
+  cudaStream_t s = (cudaStream_t)stream;
+  const bool narrow = d->input_size <= 16;
+  rc = B200RNN_EINVAL;
+  switch (ng) {
+    case 1: rc = narrow ? launch_bwd<12, 1>(a, n_cta, s) : launch_bwd<16, 1>(a, n_cta, s); break;
+    case 2: rc = narrow ? launch_bwd<12, 2>(a, n_cta, s) : launch_bwd<16, 2>(a, n_cta, s); break;
+    case 3: rc = narrow ? launch_bwd<12, 3>(a, n_cta, s) : launch_bwd<16, 3>(a, n_cta, s); break;
+    case 4: rc = narrow ? launch_bwd<12, 4>(a, n_cta, s) : launch_bwd<16, 4>(a, n_cta, s); break;
+    default: set_error("lstm_bwd_static: internal tiling error (ng=%d)", ng); break;
+  }
+  if (rc != B200RNN_OK) return rc;
+  // fixed-order sum of the rows into the caller's gradient vector (a kernel launch, no allocation)
+  return b200rnn_reduce_rows(scratch, n_cta, a.row_floats, grad_out, 0, stream);
+}

@@ -104,6 +104,34 @@ int b200rnn_lstm_bwd(const b200rnn_model_desc* d, const float* params,
                      float loss_scale, const float* d_out, const float* d_hn,
                      const float* d_cn, float* scratch, void* stream);
 
+/* Capacity of the scratch array compiled into the library for b200rnn_lstm_bwd_static. */
+#define B200RNN_STATIC_SCRATCH_FLOATS (4 * 1024 * 1024)
+
+/* Backward for callers that cannot supply scratch memory.  (No counterpart in the reference:
+ * it never manages device memory.)  Meant for hosts of this C ABI that have no allocator to
+ * ask: a plain C/C++ program without torch, a process whose own pool already owns the whole
+ * GPU so that cudaMalloc fails, or a loop that cannot afford the device-wide stall of
+ * cudaMalloc/cudaFree.  Same arguments and math as b200rnn_lstm_bwd followed by
+ * b200rnn_reduce_rows, except that the per-CTA gradient rows and the inter-layer dx buffers
+ * sit in a B200RNN_STATIC_SCRATCH_FLOATS-float (16 MiB) array inside the library, and the
+ * result is written to grad_out[n_params + 2] (gradients in torch parameter order, then the
+ * sum of per-sample losses and the correct count).  The call makes no cudaMalloc/cudaFree and
+ * calls no allocating library routine; inputs and grad_out remain the caller's.
+ *  - Every GPU that loads the library holds those 16 MiB until the process exits.
+ *  - Shapes with b200rnn_rnn_bwd_scratch_floats(d) > B200RNN_STATIC_SCRATCH_FLOATS are
+ *    refused with B200RNN_ETOOBIG (message in b200rnn_last_error()); use b200rnn_lstm_bwd.
+ *  - The first call on each device looks up the array's device address
+ *    (cudaGetSymbolAddress with that device current) and caches it; make that first call
+ *    outside any stream capture.  Later calls only launch kernels.
+ *  - All calls on a device share the one array and it keeps the previous call's contents.
+ *    Nothing in it needs clearing (each element is written before it is read within a call),
+ *    but two calls that overlap on the GPU (different streams, no dependency) race on it:
+ *    keep calls on one stream or order them with events. */
+int b200rnn_lstm_bwd_static(const b200rnn_model_desc* d, const float* params,
+                            const float* x, const float* stash, const int64_t* labels,
+                            float loss_scale, const float* d_out, const float* d_hn,
+                            const float* d_cn, float* grad_out, void* stream);
+
 /* out[i] (+)= sum_r rows[r][i] in fixed row order (deterministic). */
 int b200rnn_reduce_rows(const float* rows, int32_t n_rows, int64_t row_floats,
                         float* out, int32_t accumulate, void* stream);
