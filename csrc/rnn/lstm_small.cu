@@ -63,6 +63,27 @@ __device__ __forceinline__ float group_sum(float v) {
   return v;
 }
 
+// s[si][q]: partial gate sums (q = gate) of sample si held by each of the KQ lanes of a hidden
+// unit.  On return lane kq holds in p[q] the full sums of sample kq.
+template <int KQ>
+__device__ __forceinline__ void group_transpose_reduce(float (&s)[KQ][4], int kq, float (&p)[4]) {
+  static_assert(KQ == 4, "written for 4 lanes per hidden unit");
+  const bool hi = (kq & 2) != 0, lo = (kq & 1) != 0;
+  float k0[4], k1[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float send0 = hi ? s[0][q] : s[2][q];
+    const float send1 = hi ? s[1][q] : s[3][q];
+    k0[q] = (hi ? s[2][q] : s[0][q]) + __shfl_xor_sync(0xffffffffu, send0, 2);
+    k1[q] = (hi ? s[3][q] : s[1][q]) + __shfl_xor_sync(0xffffffffu, send1, 2);
+  }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const float send = lo ? k0[q] : k1[q];
+    p[q] = (lo ? k1[q] : k0[q]) + __shfl_xor_sync(0xffffffffu, send, 1);
+  }
+}
+
 // ---------------------------------------------------------------------------
 // Forward, one layer.  vs = [2][BTMAX][VS_LD] operand staging (double buffered).
 // ---------------------------------------------------------------------------
@@ -126,7 +147,9 @@ __device__ __forceinline__ void fwd_layer(
 
   load_inputs(0);
   store_inputs(0);
-  for (int idx = tid; idx < BTMAX * H; idx += NT) vs[(idx / H) * VS_LD + INP + (idx % H)] = 0.0f;
+  // all rows of both buffers start finite (rows >= BTc are computed but never used)
+  for (int idx = tid; idx < 2 * BTMAX * VS_LD; idx += NT)
+    if ((idx % VS_LD) >= INP || idx >= BTMAX * VS_LD) vs[idx] = 0.0f;
   float c_reg[NG];
 #pragma unroll
   for (int g = 0; g < NG; ++g) c_reg[g] = 0.0f;
@@ -137,40 +160,32 @@ __device__ __forceinline__ void fwd_layer(
     if (t + 1 < T) load_inputs(t + 1);
 #pragma unroll
     for (int g = 0; g < NG; ++g) {
+      // branch-free: the KQ samples of a group form 4*KQ independent FMA chains (ILP);
+      // rows past the tile end hold zeros and their results are simply not used.
       float s[KQ][4];
 #pragma unroll
       for (int si = 0; si < KQ; ++si) {
         const int b = g * KQ + si;
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-        if (b < BTc) {  // warp-uniform
-          const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + kq * KPT]);
+        const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + kq * KPT]);
 #pragma unroll
-          for (int j4 = 0; j4 < KPT / 4; ++j4) {
-            const float4 v = vp[j4];
-            a0 = fmaf(w[0][4 * j4 + 0], v.x, a0); a0 = fmaf(w[0][4 * j4 + 1], v.y, a0);
-            a0 = fmaf(w[0][4 * j4 + 2], v.z, a0); a0 = fmaf(w[0][4 * j4 + 3], v.w, a0);
-            a1 = fmaf(w[1][4 * j4 + 0], v.x, a1); a1 = fmaf(w[1][4 * j4 + 1], v.y, a1);
-            a1 = fmaf(w[1][4 * j4 + 2], v.z, a1); a1 = fmaf(w[1][4 * j4 + 3], v.w, a1);
-            a2 = fmaf(w[2][4 * j4 + 0], v.x, a2); a2 = fmaf(w[2][4 * j4 + 1], v.y, a2);
-            a2 = fmaf(w[2][4 * j4 + 2], v.z, a2); a2 = fmaf(w[2][4 * j4 + 3], v.w, a2);
-            a3 = fmaf(w[3][4 * j4 + 0], v.x, a3); a3 = fmaf(w[3][4 * j4 + 1], v.y, a3);
-            a3 = fmaf(w[3][4 * j4 + 2], v.z, a3); a3 = fmaf(w[3][4 * j4 + 3], v.w, a3);
-          }
+        for (int j4 = 0; j4 < KPT / 4; ++j4) {
+          const float4 v = vp[j4];
+          a0 = fmaf(w[0][4 * j4 + 0], v.x, a0); a1 = fmaf(w[1][4 * j4 + 0], v.x, a1);
+          a2 = fmaf(w[2][4 * j4 + 0], v.x, a2); a3 = fmaf(w[3][4 * j4 + 0], v.x, a3);
+          a0 = fmaf(w[0][4 * j4 + 1], v.y, a0); a1 = fmaf(w[1][4 * j4 + 1], v.y, a1);
+          a2 = fmaf(w[2][4 * j4 + 1], v.y, a2); a3 = fmaf(w[3][4 * j4 + 1], v.y, a3);
+          a0 = fmaf(w[0][4 * j4 + 2], v.z, a0); a1 = fmaf(w[1][4 * j4 + 2], v.z, a1);
+          a2 = fmaf(w[2][4 * j4 + 2], v.z, a2); a3 = fmaf(w[3][4 * j4 + 2], v.z, a3);
+          a0 = fmaf(w[0][4 * j4 + 3], v.w, a0); a1 = fmaf(w[1][4 * j4 + 3], v.w, a1);
+          a2 = fmaf(w[2][4 * j4 + 3], v.w, a2); a3 = fmaf(w[3][4 * j4 + 3], v.w, a3);
         }
         s[si][0] = a0; s[si][1] = a1; s[si][2] = a2; s[si][3] = a3;
       }
-      // butterfly over the KQ lanes of this hidden unit, then lane kq keeps sample g*KQ+kq
+      // transpose-reduce over the KQ lanes of this hidden unit: lane kq ends with the 4 gate
+      // sums of sample g*KQ + kq (12 shuffles instead of 32 for a full butterfly)
       float p[4];
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        float mine = 0.0f;
-#pragma unroll
-        for (int si = 0; si < KQ; ++si) {
-          const float r = group_sum<KQ>(s[si][q]);
-          if (si == kq) mine = r;
-        }
-        p[q] = mine;
-      }
+      group_transpose_reduce<KQ>(s, kq, p);
       const int b = g * KQ + kq;
       if (b < BTc) {
         const float ig = sigmoid_f(p[0] + bias[0]);
@@ -219,7 +234,13 @@ __global__ void __launch_bounds__(H* KQ) lstm_fwd_kernel(const FwdArgs a) {
 }
 
 // ---------------------------------------------------------------------------
-// Backward, one layer.
+// Backward, one layer.  Warp-specialised: the CTA has 2*NT threads.
+//   role 0 ("A", threads 0..NT-1, mapping tid = u*KQ + kq): gate gradients (phase A) and the
+//           dW += dG^T [x_t | h_{t-1}] accumulation in registers (phase B2);
+//   role 1 ("B", threads NT..2NT-1, mapping tid = k*JQ + jq): dv = dG x [W_ih | W_hh] with the
+//           W^T slice in registers (phase B1: dh for step t-1 — the serial chain — and dx for the
+//           layer below), plus the prefetch/staging of the next step's operands.
+// B1 and B2 run concurrently on different warps; two __syncthreads per step.
 // ---------------------------------------------------------------------------
 template <int H, int KQ, int KPT, int NG, bool HAS_DX>
 __device__ __forceinline__ void bwd_layer(
@@ -247,183 +268,193 @@ __device__ __forceinline__ void bwd_layer(
   static_assert(NT % NOUT == 0 && JQ >= 1 && (JQ & (JQ - 1)) == 0 && JR % 4 == 0, "bad B mapping");
   static_assert(!HAS_DX || INP == H, "dx only for stacked layers (input width == H)");
 
-  const int tid = threadIdx.x;
+  const bool roleA = threadIdx.x < NT;
+  const int tid = roleA ? threadIdx.x : threadIdx.x - NT;   // role-local id
   const int u = tid / KQ, kq = tid % KQ;       // A mapping
   const int kB = tid / JQ, jq = tid % JQ;      // B mapping
 
-  // W^T slice for the B mapping: wt[jj] = Wcat[row(j')][KOFF + kB], j' = jq*JR + jj = u'*4 + g'
-  float wt[JR];
+  if (roleA) {
+    // =========================== role A ===========================
+    float dW[4][KPT];
 #pragma unroll
-  for (int jj = 0; jj < JR; ++jj) {
-    const int jp = jq * JR + jj;
-    const int up = jp >> 2, gp = jp & 3;
-    const int r = gp * H + up;
-    const int kk = KOFF + kB;
-    float v;
-    if (kk < INP) v = (kk < in_dim) ? w_ih[(int64_t)r * in_dim + kk] : 0.0f;
-    else v = w_hh[(int64_t)r * H + (kk - INP)];
-    wt[jj] = v;
-  }
-
-  float dW[4][KPT];
+    for (int g = 0; g < 4; ++g)
 #pragma unroll
-  for (int g = 0; g < 4; ++g)
+      for (int j = 0; j < KPT; ++j) dW[g][j] = 0.0f;
+    float dbacc[4] = {0.f, 0.f, 0.f, 0.f};
+    float dc_reg[NG], c_t[NG], pf_cprev[NG], pf_da[NG];
+    float4 pf_g[NG];
+
+    auto load_step = [&](int t) {  // stash values phase A of step t needs
 #pragma unroll
-    for (int j = 0; j < KPT; ++j) dW[g][j] = 0.0f;
-  float dbacc[4] = {0.f, 0.f, 0.f, 0.f};
-
-  // per-slot carries / prefetch registers (slot g <-> sample g*KQ + kq)
-  float dc_reg[NG], c_t[NG], pf_cprev[NG], pf_da[NG];
-  float4 pf_g[NG];
-  float pfx[NPFX], pfh[NPFH];
-
-  auto load_step = [&](int t) {  // everything step t needs from global
+      for (int g = 0; g < NG; ++g) {
+        const int b = g * KQ + kq;
+        float4 gv = make_float4(0.f, 0.f, 0.f, 0.f);
+        float cp = 0.f, da = 0.f;
+        if (b < BTc) {
+          const int64_t e = ((int64_t)t * B + (b0 + b)) * H + u;
+          gv = reinterpret_cast<const float4*>(g_seq)[e];
+          if (t > 0) cp = c_seq[e - (int64_t)B * H];
+          if (dabove != nullptr) da = dabove[(int64_t)(b0 + b) * da_sb + (int64_t)t * da_st + u];
+        }
+        pf_g[g] = gv; pf_cprev[g] = cp; pf_da[g] = da;
+      }
+    };
 #pragma unroll
     for (int g = 0; g < NG; ++g) {
       const int b = g * KQ + kq;
-      float4 gv = make_float4(0.f, 0.f, 0.f, 0.f);
-      float cp = 0.f, da = 0.f;
+      float ct = 0.f, dc = 0.f;
       if (b < BTc) {
-        const int64_t e = ((int64_t)t * B + (b0 + b)) * H + u;
-        gv = reinterpret_cast<const float4*>(g_seq)[e];
-        if (t > 0) cp = c_seq[e - (int64_t)B * H];
-        if (dabove != nullptr) da = dabove[(int64_t)(b0 + b) * da_sb + (int64_t)t * da_st + u];
+        const int64_t e = ((int64_t)(T - 1) * B + (b0 + b)) * H + u;
+        ct = c_seq[e];
+        if (d_cn != nullptr) dc = d_cn[(int64_t)(b0 + b) * H + u];
       }
-      pf_g[g] = gv; pf_cprev[g] = cp; pf_da[g] = da;
+      c_t[g] = ct; dc_reg[g] = dc;
     }
-#pragma unroll
-    for (int i = 0; i < NPFX; ++i) {
-      const int idx = tid + i * NT;
-      const int b = idx / INP, k = idx % INP;
-      float v = 0.0f;
-      if (idx < BTMAX * INP && b < BTc && k < in_dim)
-        v = inp[(int64_t)(b0 + b) * in_sb + (int64_t)t * in_st + k];
-      pfx[i] = v;
-    }
-#pragma unroll
-    for (int i = 0; i < NPFH; ++i) {
-      const int idx = tid + i * NT;
-      const int b = idx / H, k = idx % H;
-      float v = 0.0f;
-      if (idx < BTMAX * H && b < BTc && t > 0)
-        v = h_seq[((int64_t)(t - 1) * B + (b0 + b)) * H + k];
-      pfh[i] = v;
-    }
-  };
-  auto store_operands = [&](int buf) {
-#pragma unroll
-    for (int i = 0; i < NPFX; ++i) {
-      const int idx = tid + i * NT;
-      if (idx < BTMAX * INP) vs[(buf * BTMAX + idx / INP) * VS_LD + (idx % INP)] = pfx[i];
-    }
-#pragma unroll
-    for (int i = 0; i < NPFH; ++i) {
-      const int idx = tid + i * NT;
-      if (idx < BTMAX * H) vs[(buf * BTMAX + idx / H) * VS_LD + INP + (idx % H)] = pfh[i];
-    }
-  };
+    load_step(T - 1);
+    __syncthreads();  // (S0) operands of step T-1 staged by role B; caller's dhrec_s init visible
 
-  // initial carries
+    for (int t = T - 1; t >= 0; --t) {
+      const int cur = t & 1;
+      float4 gv[NG]; float cprev[NG], da[NG];
 #pragma unroll
-  for (int g = 0; g < NG; ++g) {
-    const int b = g * KQ + kq;
-    float ct = 0.f, dc = 0.f;
-    if (b < BTc) {
-      const int64_t e = ((int64_t)(T - 1) * B + (b0 + b)) * H + u;
-      ct = c_seq[e];
-      if (d_cn != nullptr) dc = d_cn[(int64_t)(b0 + b) * H + u];
-    }
-    c_t[g] = ct; dc_reg[g] = dc;
-  }
-  load_step(T - 1);
-  store_operands((T - 1) & 1);
-  __syncthreads();  // also orders the caller's dhrec_s initialisation
-
-  for (int t = T - 1; t >= 0; --t) {
-    const int cur = t & 1, nxt = cur ^ 1;
-    // consume the prefetched step-t values, then immediately prefetch step t-1
-    float4 gv[NG]; float cprev[NG], da[NG];
+      for (int g = 0; g < NG; ++g) { gv[g] = pf_g[g]; cprev[g] = pf_cprev[g]; da[g] = pf_da[g]; }
+      if (t > 0) load_step(t - 1);
+      // ---- phase A: gate gradients for my (sample, unit) slots ----
 #pragma unroll
-    for (int g = 0; g < NG; ++g) { gv[g] = pf_g[g]; cprev[g] = pf_cprev[g]; da[g] = pf_da[g]; }
-    if (t > 0) load_step(t - 1);
-
-    // ---- phase A: gate gradients for my (sample, unit) slots ----
-#pragma unroll
-    for (int g = 0; g < NG; ++g) {
-      const int b = g * KQ + kq;
-      if (b < BTc) {
-        const float ig = gv[g].x, fg = gv[g].y, gg = gv[g].z, og = gv[g].w;
-        const float dh = dhrec_s[b * H + u] + da[g];
-        const float tc = tanh_f(c_t[g]);
-        const float dct = fmaf(dh * og, 1.0f - tc * tc, dc_reg[g]);
-        const float dpi = dct * gg * ig * (1.0f - ig);
-        const float dpf = dct * cprev[g] * fg * (1.0f - fg);
-        const float dpg = dct * ig * (1.0f - gg * gg);
-        const float dpo = dh * tc * og * (1.0f - og);
-        dc_reg[g] = dct * fg;
-        c_t[g] = cprev[g];
-        reinterpret_cast<float4*>(dG_s)[b * H + u] = make_float4(dpi, dpf, dpg, dpo);
-        dbacc[0] += dpi; dbacc[1] += dpf; dbacc[2] += dpg; dbacc[3] += dpo;
+      for (int g = 0; g < NG; ++g) {
+        const int b = g * KQ + kq;
+        if (b < BTc) {
+          const float ig = gv[g].x, fg = gv[g].y, gg = gv[g].z, og = gv[g].w;
+          const float dh = dhrec_s[b * H + u] + da[g];
+          const float tc = tanh_f(c_t[g]);
+          const float dct = fmaf(dh * og, 1.0f - tc * tc, dc_reg[g]);
+          const float dpi = dct * gg * ig * (1.0f - ig);
+          const float dpf = dct * cprev[g] * fg * (1.0f - fg);
+          const float dpg = dct * ig * (1.0f - gg * gg);
+          const float dpo = dh * tc * og * (1.0f - og);
+          dc_reg[g] = dct * fg;
+          c_t[g] = cprev[g];
+          reinterpret_cast<float4*>(dG_s)[b * H + u] = make_float4(dpi, dpf, dpg, dpo);
+          dbacc[0] += dpi; dbacc[1] += dpf; dbacc[2] += dpg; dbacc[3] += dpo;
+        }
       }
+      __syncthreads();  // (S1) dG_s complete
+      // ---- phase B2: dW += dG^T [x_t | h_{t-1}] ----
+#pragma unroll 2
+      for (int b = 0; b < BTc; ++b) {
+        const float4 d = reinterpret_cast<const float4*>(dG_s)[b * H + u];
+        const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + kq * KPT]);
+#pragma unroll
+        for (int j4 = 0; j4 < KPT / 4; ++j4) {
+          const float4 v = vp[j4];
+          dW[0][4 * j4 + 0] = fmaf(d.x, v.x, dW[0][4 * j4 + 0]); dW[0][4 * j4 + 1] = fmaf(d.x, v.y, dW[0][4 * j4 + 1]);
+          dW[0][4 * j4 + 2] = fmaf(d.x, v.z, dW[0][4 * j4 + 2]); dW[0][4 * j4 + 3] = fmaf(d.x, v.w, dW[0][4 * j4 + 3]);
+          dW[1][4 * j4 + 0] = fmaf(d.y, v.x, dW[1][4 * j4 + 0]); dW[1][4 * j4 + 1] = fmaf(d.y, v.y, dW[1][4 * j4 + 1]);
+          dW[1][4 * j4 + 2] = fmaf(d.y, v.z, dW[1][4 * j4 + 2]); dW[1][4 * j4 + 3] = fmaf(d.y, v.w, dW[1][4 * j4 + 3]);
+          dW[2][4 * j4 + 0] = fmaf(d.z, v.x, dW[2][4 * j4 + 0]); dW[2][4 * j4 + 1] = fmaf(d.z, v.y, dW[2][4 * j4 + 1]);
+          dW[2][4 * j4 + 2] = fmaf(d.z, v.z, dW[2][4 * j4 + 2]); dW[2][4 * j4 + 3] = fmaf(d.z, v.w, dW[2][4 * j4 + 3]);
+          dW[3][4 * j4 + 0] = fmaf(d.w, v.x, dW[3][4 * j4 + 0]); dW[3][4 * j4 + 1] = fmaf(d.w, v.y, dW[3][4 * j4 + 1]);
+          dW[3][4 * j4 + 2] = fmaf(d.w, v.z, dW[3][4 * j4 + 2]); dW[3][4 * j4 + 3] = fmaf(d.w, v.w, dW[3][4 * j4 + 3]);
+        }
+      }
+      __syncthreads();  // (S2) dhrec_s / next operands ready (role B); dG_s, vs[cur] free
     }
-    __syncthreads();
+    // ---- emit this CTA's partial gradients (torch parameter layout) ----
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const int r = g * H + u;
+#pragma unroll
+      for (int j = 0; j < KPT; ++j) {
+        const int k = kq * KPT + j;
+        if (k < INP) { if (k < in_dim) row[off_wih + (int64_t)r * in_dim + k] = dW[g][j]; }
+        else row[off_whh + (int64_t)r * H + (k - INP)] = dW[g][j];
+      }
+      const float db = group_sum<KQ>(dbacc[g]);
+      if (kq == 0) { row[off_bih + r] = db; row[off_bhh + r] = db; }
+    }
+  } else {
+    // =========================== role B ===========================
+    // W^T slice: wt[jj] = Wcat[row(j')][KOFF + kB], j' = jq*JR + jj = u'*4 + g'
+    float wt[JR];
+#pragma unroll
+    for (int jj = 0; jj < JR; ++jj) {
+      const int jp = jq * JR + jj;
+      const int up = jp >> 2, gp = jp & 3;
+      const int r = gp * H + up;
+      const int kk = KOFF + kB;
+      float v;
+      if (kk < INP) v = (kk < in_dim) ? w_ih[(int64_t)r * in_dim + kk] : 0.0f;
+      else v = w_hh[(int64_t)r * H + (kk - INP)];
+      wt[jj] = v;
+    }
+    float pfx[NPFX], pfh[NPFH];
+    auto load_operands = [&](int t) {  // [x_t | h_{t-1}] of my tile
+#pragma unroll
+      for (int i = 0; i < NPFX; ++i) {
+        const int idx = tid + i * NT;
+        const int b = idx / INP, k = idx % INP;
+        float v = 0.0f;
+        if (idx < BTMAX * INP && b < BTc && k < in_dim)
+          v = inp[(int64_t)(b0 + b) * in_sb + (int64_t)t * in_st + k];
+        pfx[i] = v;
+      }
+#pragma unroll
+      for (int i = 0; i < NPFH; ++i) {
+        const int idx = tid + i * NT;
+        const int b = idx / H, k = idx % H;
+        float v = 0.0f;
+        if (idx < BTMAX * H && b < BTc && t > 0)
+          v = h_seq[((int64_t)(t - 1) * B + (b0 + b)) * H + k];
+        pfh[i] = v;
+      }
+    };
+    auto store_operands = [&](int buf) {
+#pragma unroll
+      for (int i = 0; i < NPFX; ++i) {
+        const int idx = tid + i * NT;
+        if (idx < BTMAX * INP) vs[(buf * BTMAX + idx / INP) * VS_LD + (idx % INP)] = pfx[i];
+      }
+#pragma unroll
+      for (int i = 0; i < NPFH; ++i) {
+        const int idx = tid + i * NT;
+        if (idx < BTMAX * H) vs[(buf * BTMAX + idx / H) * VS_LD + INP + (idx % H)] = pfh[i];
+      }
+    };
+    load_operands(T - 1);
+    store_operands((T - 1) & 1);
+    __syncthreads();  // (S0)
 
-    // ---- phase B1: dv = dG x [W_ih | W_hh]  (dx for the layer below, dh for step t-1) ----
-    for (int b = 0; b < BTc; ++b) {
-      const float4* dp = reinterpret_cast<const float4*>(&dG_s[b * G4 + jq * JR]);
-      float acc = 0.0f;
+    for (int t = T - 1; t >= 0; --t) {
+      const int nxt = (t & 1) ^ 1;
+      if (t > 0) load_operands(t - 1);   // global loads in flight across the barrier
+      __syncthreads();  // (S1) dG_s complete
+      // ---- phase B1: dv = dG x [W_ih | W_hh]  (dx for the layer below, dh for step t-1) ----
+#pragma unroll 2
+      for (int b = 0; b < BTc; ++b) {
+        const float4* dp = reinterpret_cast<const float4*>(&dG_s[b * G4 + jq * JR]);
+        float acc0 = 0.0f, acc1 = 0.0f, acc2 = 0.0f, acc3 = 0.0f;  // 4 independent chains per sample
 #pragma unroll
-      for (int j4 = 0; j4 < JR / 4; ++j4) {
-        const float4 d = dp[j4];
-        acc = fmaf(wt[4 * j4 + 0], d.x, acc); acc = fmaf(wt[4 * j4 + 1], d.y, acc);
-        acc = fmaf(wt[4 * j4 + 2], d.z, acc); acc = fmaf(wt[4 * j4 + 3], d.w, acc);
+        for (int j4 = 0; j4 < JR / 4; ++j4) {
+          const float4 d = dp[j4];
+          acc0 = fmaf(wt[4 * j4 + 0], d.x, acc0); acc1 = fmaf(wt[4 * j4 + 1], d.y, acc1);
+          acc2 = fmaf(wt[4 * j4 + 2], d.z, acc2); acc3 = fmaf(wt[4 * j4 + 3], d.w, acc3);
+        }
+        const float acc = group_sum<JQ>((acc0 + acc1) + (acc2 + acc3));
+        if (jq == 0) {
+          const int kk = KOFF + kB;
+          if (HAS_DX && kk < INP) dx_out[((int64_t)t * B + (b0 + b)) * H + kk] = acc;
+          else dhrec_s[b * H + (kk - INP)] = acc;
+        }
       }
-      acc = group_sum<JQ>(acc);
-      if (jq == 0) {
-        const int kk = KOFF + kB;
-        if (HAS_DX && kk < INP) dx_out[((int64_t)t * B + (b0 + b)) * H + kk] = acc;
-        else dhrec_s[b * H + (kk - INP)] = acc;
-      }
+      if (t > 0) store_operands(nxt);
+      __syncthreads();  // (S2)
     }
-    // ---- phase B2: dW += dG^T [x_t | h_{t-1}] (register accumulators, A mapping) ----
-    for (int b = 0; b < BTc; ++b) {
-      const float4 d = reinterpret_cast<const float4*>(dG_s)[b * H + u];
-      const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + kq * KPT]);
-#pragma unroll
-      for (int j4 = 0; j4 < KPT / 4; ++j4) {
-        const float4 v = vp[j4];
-        dW[0][4 * j4 + 0] = fmaf(d.x, v.x, dW[0][4 * j4 + 0]); dW[0][4 * j4 + 1] = fmaf(d.x, v.y, dW[0][4 * j4 + 1]);
-        dW[0][4 * j4 + 2] = fmaf(d.x, v.z, dW[0][4 * j4 + 2]); dW[0][4 * j4 + 3] = fmaf(d.x, v.w, dW[0][4 * j4 + 3]);
-        dW[1][4 * j4 + 0] = fmaf(d.y, v.x, dW[1][4 * j4 + 0]); dW[1][4 * j4 + 1] = fmaf(d.y, v.y, dW[1][4 * j4 + 1]);
-        dW[1][4 * j4 + 2] = fmaf(d.y, v.z, dW[1][4 * j4 + 2]); dW[1][4 * j4 + 3] = fmaf(d.y, v.w, dW[1][4 * j4 + 3]);
-        dW[2][4 * j4 + 0] = fmaf(d.z, v.x, dW[2][4 * j4 + 0]); dW[2][4 * j4 + 1] = fmaf(d.z, v.y, dW[2][4 * j4 + 1]);
-        dW[2][4 * j4 + 2] = fmaf(d.z, v.z, dW[2][4 * j4 + 2]); dW[2][4 * j4 + 3] = fmaf(d.z, v.w, dW[2][4 * j4 + 3]);
-        dW[3][4 * j4 + 0] = fmaf(d.w, v.x, dW[3][4 * j4 + 0]); dW[3][4 * j4 + 1] = fmaf(d.w, v.y, dW[3][4 * j4 + 1]);
-        dW[3][4 * j4 + 2] = fmaf(d.w, v.z, dW[3][4 * j4 + 2]); dW[3][4 * j4 + 3] = fmaf(d.w, v.w, dW[3][4 * j4 + 3]);
-      }
-    }
-    if (t > 0) store_operands(nxt);
-    __syncthreads();
-  }
-
-  // ---- emit this CTA's partial gradients (torch parameter layout) ----
-#pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    const int r = g * H + u;
-#pragma unroll
-    for (int j = 0; j < KPT; ++j) {
-      const int k = kq * KPT + j;
-      if (k < INP) { if (k < in_dim) row[off_wih + (int64_t)r * in_dim + k] = dW[g][j]; }
-      else row[off_whh + (int64_t)r * H + (k - INP)] = dW[g][j];
-    }
-    const float db = group_sum<KQ>(dbacc[g]);
-    if (kq == 0) { row[off_bih + r] = db; row[off_bhh + r] = db; }
   }
 }
 
 template <int H, int KQ, int KPT0, int NG>
-__global__ void __launch_bounds__(H* KQ) lstm_bwd_kernel(const BwdArgs a) {
-  constexpr int NT = H * KQ;
+__global__ void __launch_bounds__(2 * H * KQ, 2) lstm_bwd_kernel(const BwdArgs a) {
+  constexpr int NT2 = 2 * H * KQ;   // all threads (both roles)
   constexpr int KPT1 = 2 * H / KQ;
   constexpr int BTMAX = NG * KQ;
   constexpr int VS_LD = 2 * H + 4;
@@ -448,10 +479,10 @@ __global__ void __launch_bounds__(H* KQ) lstm_bwd_kernel(const BwdArgs a) {
     const float* fcw = a.params + a.off_fcw;
     const float* fcb = a.params + a.off_fcb;
     float* hT = dG_s;  // reuse: [BTMAX][H]
-    for (int idx = tid; idx < BTc * H; idx += NT)
+    for (int idx = tid; idx < BTc * H; idx += NT2)
       hT[idx] = a.h_seq[(L - 1) * lsz + ((int64_t)(a.T - 1) * a.B + (b0 + idx / H)) * H + (idx % H)];
     __syncthreads();
-    for (int idx = tid; idx < BTc * C; idx += NT) {
+    for (int idx = tid; idx < BTc * C; idx += NT2) {
       const int b = idx / C, c = idx % C;
       float acc = fcb[c];
 #pragma unroll 8
@@ -482,31 +513,31 @@ __global__ void __launch_bounds__(H* KQ) lstm_bwd_kernel(const BwdArgs a) {
       if (tid == 0) { row[a.n_params] = loss_b; row[a.n_params + 1] = corr_b; }
     }
     __syncthreads();
-    for (int idx = tid; idx < BTc * H; idx += NT) {
+    for (int idx = tid; idx < BTc * H; idx += NT2) {
       const int b = idx / H, k = idx % H;
       float acc = 0.f;
       for (int c = 0; c < C; ++c) acc = fmaf(lg_s[b * CMAX + c], fcw[c * H + k], acc);
       if (a.d_hn != nullptr) acc += a.d_hn[((int64_t)(L - 1) * a.B + (b0 + b)) * H + k];
       dhrec_s[idx] = acc;
     }
-    for (int idx = tid; idx < C * H; idx += NT) {
+    for (int idx = tid; idx < C * H; idx += NT2) {
       const int c = idx / H, k = idx % H;
       float acc = 0.f;
       for (int b = 0; b < BTc; ++b) acc = fmaf(lg_s[b * CMAX + c], hT[b * H + k], acc);
       row[a.off_fcw + idx] = acc;
     }
-    for (int c = tid; c < C; c += NT) {
+    for (int c = tid; c < C; c += NT2) {
       float acc = 0.f;
       for (int b = 0; b < BTc; ++b) acc += lg_s[b * CMAX + c];
       row[a.off_fcb + c] = acc;
     }
     __syncthreads();  // hT (aliases dG_s) fully consumed before phase A overwrites it
   } else {
-    for (int idx = tid; idx < BTc * H; idx += NT)
+    for (int idx = tid; idx < BTc * H; idx += NT2)
       dhrec_s[idx] = (a.d_hn != nullptr) ? a.d_hn[((int64_t)(L - 1) * a.B + (b0 + idx / H)) * H + (idx % H)] : 0.f;
     if (a.C > 0) {
-      for (int idx = tid; idx < a.C * H; idx += NT) row[a.off_fcw + idx] = 0.f;
-      for (int c = tid; c < a.C; c += NT) row[a.off_fcb + c] = 0.f;
+      for (int idx = tid; idx < a.C * H; idx += NT2) row[a.off_fcw + idx] = 0.f;
+      for (int c = tid; c < a.C; c += NT2) row[a.off_fcb + c] = 0.f;
     }
     if (tid == 0) { row[a.n_params] = 0.f; row[a.n_params + 1] = 0.f; }
   }
@@ -525,7 +556,7 @@ __global__ void __launch_bounds__(H* KQ) lstm_bwd_kernel(const BwdArgs a) {
         row, a.off_wih[l], a.off_whh[l], a.off_bih[l], a.off_bhh[l],
         a.T, a.B, b0, BTc, vs, dG_s, dhrec_s);
     __syncthreads();  // dx tile of layer l visible; smem free for reuse
-    for (int idx = tid; idx < BTc * H; idx += NT)
+    for (int idx = tid; idx < BTc * H; idx += NT2)
       dhrec_s[idx] = (a.d_hn != nullptr) ? a.d_hn[((int64_t)(l - 1) * a.B + (b0 + idx / H)) * H + (idx % H)] : 0.f;
   }
   {
@@ -548,8 +579,25 @@ __global__ void __launch_bounds__(H* KQ) lstm_bwd_kernel(const BwdArgs a) {
 // ---------------------------------------------------------------------------
 constexpr int kH = 32, kKQ = 4;
 
+// Rows per CTA.  Forward tiles are multiples of KQ (its sample groups are KQ wide and computed
+// branch-free); pick the tile that minimises the per-SM load when CTAs spread evenly with at most
+// `slots` co-resident CTAs per SM (register-limited), smaller tile on ties (more warps per SM).
+int choose_bt_fwd(int B) {
+  const int sms = num_sms(), slots = 4;
+  int best = 4, best_load = 1 << 30;
+  for (int bt = 4; bt <= kMaxBT; bt += 4) {
+    const int n = (B + bt - 1) / bt;
+    const int per_sm = (n + sms - 1) / sms;
+    const int waves = (per_sm + slots - 1) / slots;
+    const int load = waves * slots >= per_sm && waves == 1 ? per_sm * bt : waves * slots * bt;
+    if (load < best_load) { best_load = load; best = bt; }
+  }
+  return best;
+}
+// Backward loops over samples with a runtime bound, so any tile size works: two CTAs per SM
+// (its register budget), i.e. 4 warps per scheduler.
 int choose_bt(int B) {
-  int bt = (B + num_sms() - 1) / num_sms();
+  int bt = (B + 2 * num_sms() - 1) / (2 * num_sms());
   if (bt < 1) bt = 1;
   if (bt > kMaxBT) bt = kMaxBT;
   return bt;
@@ -569,7 +617,7 @@ int launch_fwd(const FwdArgs& a, int n_cta, cudaStream_t s) {
 }
 template <int KPT0, int NG>
 int launch_bwd(const BwdArgs& a, int n_cta, cudaStream_t s) {
-  lstm_bwd_kernel<kH, kKQ, KPT0, NG><<<n_cta, kH * kKQ, 0, s>>>(a);
+  lstm_bwd_kernel<kH, kKQ, KPT0, NG><<<n_cta, 2 * kH * kKQ, 0, s>>>(a);
   B200_CHECK_LAUNCH();
   return B200RNN_OK;
 }
@@ -622,7 +670,7 @@ extern "C" int b200rnn_lstm_fwd(const b200rnn_model_desc* d, const float* params
     a.off_bih[l] = d->off_bih[l]; a.off_bhh[l] = d->off_bhh[l];
   }
   a.I = d->input_size; a.T = d->seq_len; a.B = d->batch; a.L = d->num_layers;
-  a.BT = choose_bt(d->batch); a.training = training;
+  a.BT = choose_bt_fwd(d->batch); a.training = training;
   const int n_cta = (a.B + a.BT - 1) / a.BT;
   const int ng = (a.BT + kKQ - 1) / kKQ;
   cudaStream_t s = (cudaStream_t)stream;
