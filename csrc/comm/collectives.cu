@@ -1,0 +1,422 @@
+// K7-K9 — collectives issued from INSIDE kernels over NVLink / NVSwitch peer memory.
+//
+// Every rank owns one symmetric region (flags | inbox | heap); every region is mapped into
+// every rank (CUDA IPC, csrc/runtime/symm.cpp), so a kernel on rank r can store straight into
+// rank p's memory and raise a flag there.  No host involvement, no NCCL: the reference's
+// equivalents are c10d Reducer -> MPI_Allreduce / MPI_Bcast / MPI_Send/Recv on CPU tensors
+// (src/motion/trainer/ddp.py:18-19, src/example/example_distributed.py:11-14) and Horovod's
+// fusion buffer + MPI allreduce (trainer/horovod.py:35).
+//
+// Protocol (all flags are monotonically increasing sequence numbers, never reset):
+//   writer : data stores to the peer -> __threadfence_system -> bar.sync -> st.release.sys flag
+//   reader : ld.acquire.sys spin on its OWN memory until flag >= seq -> bar.sync -> ld.cg data
+// Inboxes are double-buffered by the parity of seq; a slot is only overwritten two calls
+// later, which the peers' own progress already orders after the last read.
+// Every spin has a clock64 watchdog that records the missing source in a status word instead
+// of hanging the GPU.  Sums are taken in rank order 0..W-1 on every rank => bit-identical
+// results everywhere (the reference's "equal final parameters" criterion, README.md:9).
+#include "../common.cuh"
+#include "../optim.cuh"
+
+namespace b200rnn {
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kElems = 4;                       // elements per thread in the two-shot kernel
+constexpr int kBlockElems = kThreads * kElems;  // 1024 parameters per two-shot block
+constexpr long long kDefaultTimeout = 4000000000LL;  // ~2 s of SM clocks
+
+struct Ctx {  // device-side view
+  int rank, world, max_blocks, delay_ns;
+  long long inbox_floats, timeout;
+  char* base[B200RNN_MAX_PEERS];
+  long long off_flags_ar, off_flags_pr, off_flags_sig, off_flags_bar, off_status, off_inbox, off_heap;
+};
+
+Ctx to_dev(const b200rnn_comm_ctx* c) {
+  Ctx d;
+  d.rank = c->rank; d.world = c->world; d.max_blocks = c->max_blocks; d.delay_ns = c->delay_ns;
+  d.inbox_floats = c->inbox_floats;
+  d.timeout = c->timeout_cycles > 0 ? c->timeout_cycles : kDefaultTimeout;
+  for (int i = 0; i < B200RNN_MAX_PEERS; ++i) d.base[i] = (char*)c->base[i];
+  d.off_flags_ar = c->off_flags_ar; d.off_flags_pr = c->off_flags_pr; d.off_flags_sig = c->off_flags_sig;
+  d.off_flags_bar = c->off_flags_bar; d.off_status = c->off_status; d.off_inbox = c->off_inbox;
+  d.off_heap = c->off_heap;
+  return d;
+}
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t* flags_ar(const Ctx& c, int owner, int src, int blk) {
+  return reinterpret_cast<uint32_t*>(c.base[owner] + c.off_flags_ar) + (long long)src * c.max_blocks + blk;
+}
+__device__ __forceinline__ uint32_t* flags_pr(const Ctx& c, int owner, int blk) {
+  return reinterpret_cast<uint32_t*>(c.base[owner] + c.off_flags_pr) + blk;
+}
+__device__ __forceinline__ float* inbox(const Ctx& c, int owner, uint32_t seq, int src) {
+  return reinterpret_cast<float*>(c.base[owner] + c.off_inbox) + ((long long)(seq & 1) * c.world + src) * c.inbox_floats;
+}
+__device__ __forceinline__ void delay(const Ctx& c) {
+  if (c.delay_ns > 0) {
+    long long t0 = clock64();
+    const long long cycles = (long long)c.delay_ns * 2;  // ~2 GHz SM clock
+    while (clock64() - t0 < cycles) { }
+  }
+}
+// Spin until *f >= seq (wrap-safe); on timeout set bit `src` in this rank's status word.
+__device__ __forceinline__ void wait_flag(const Ctx& c, const uint32_t* f, uint32_t seq, int src) {
+  const long long t0 = clock64();
+  while ((int32_t)(ld_acquire_sys(f) - seq) < 0) {
+    if (clock64() - t0 > c.timeout) {
+      atomicOr(reinterpret_cast<unsigned int*>(c.base[c.rank] + c.off_status), 1u << src);
+      return;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// One-shot: every rank pushes its whole (locally reduced) vector into every peer's inbox,
+// then sums the W inbox slices it received.  1 NVLink one-way latency; traffic W*n per rank:
+// the right trade for the 56.6 KB gradient of the reference's model.
+// Block b handles elements [b*256, (b+1)*256); flags are per (source, block), so blocks are
+// independent and no grid-wide synchronisation exists.
+// ---------------------------------------------------------------------------
+template <bool UPDATE>
+__global__ void __launch_bounds__(kThreads) oneshot_kernel(
+    Ctx c, uint32_t seq, const float* __restrict__ rows, int n_rows, long long n, long long row_stride,
+    float* buf /* UPDATE: params, else in/out vector */, float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
+    OptScalars o, float scale, float* __restrict__ metrics) {
+  const long long i = (long long)blockIdx.x * kThreads + threadIdx.x;
+  const bool live = i < n;
+  float g = 0.0f;
+  if (UPDATE) {
+    if (i < n + 2) {
+      for (int r = 0; r < n_rows; ++r) g += rows[(long long)r * row_stride + i];
+      if (i >= n && metrics != nullptr) metrics[i - n] = g;  // loss sum / correct count stay local
+    }
+  } else if (live) {
+    g = buf[i];
+  }
+  if (live) {
+    for (int p = 0; p < c.world; ++p) inbox(c, p, seq, c.rank)[i] = g;   // peer stores (incl. self)
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    delay(c);
+    for (int p = 0; p < c.world; ++p) st_release_sys(flags_ar(c, p, c.rank, blockIdx.x), seq);
+  }
+  if (threadIdx.x < c.world) wait_flag(c, flags_ar(c, c.rank, threadIdx.x, blockIdx.x), seq, threadIdx.x);
+  __syncthreads();
+  if (!live) return;
+  float sum = 0.0f;
+  for (int s = 0; s < c.world; ++s) sum += __ldcg(inbox(c, c.rank, seq, s) + i);   // fixed rank order
+  if (UPDATE) {
+    const float gg = sum * o.grad_scale;
+    float p = buf[i];
+    float m = exp_avg ? exp_avg[i] : 0.0f;
+    float v = exp_avg_sq ? exp_avg_sq[i] : 0.0f;
+    apply_update(o, gg, p, m, v);
+    buf[i] = p;
+    if (exp_avg) exp_avg[i] = m;
+    if (exp_avg_sq) exp_avg_sq[i] = v;
+  } else {
+    buf[i] = sum * scale;
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Two-shot: reduce-scatter the gradient to its owning rank, run the optimizer on the owner's
+// shard, all-gather the UPDATED PARAMETERS by peer stores into every rank's (symmetric) arena.
+// Traffic 2(W-1)/W * n per rank.  Persistent grid: block k (1024 elements) is handled by CTA
+// k mod gridDim on every rank, in increasing k, which makes the cross-rank waits deadlock-free
+// as long as the grid is co-resident (grid <= #SMs).
+// ---------------------------------------------------------------------------
+template <bool UPDATE>
+__global__ void __launch_bounds__(kThreads) twoshot_kernel(
+    Ctx c, uint32_t seq, const float* __restrict__ rows, int n_rows, long long n, long long row_stride,
+    float* buf, long long buf_heap_off, float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
+    OptScalars o, float scale, float* __restrict__ metrics, int n_blocks, int blocks_per_rank) {
+  if (UPDATE && blockIdx.x == 0 && threadIdx.x < 2 && metrics != nullptr) {
+    float g = 0.0f;
+    for (int r = 0; r < n_rows; ++r) g += rows[(long long)r * row_stride + n + threadIdx.x];
+    metrics[threadIdx.x] = g;
+  }
+  for (int k = blockIdx.x; k < n_blocks; k += gridDim.x) {
+    const int owner = k / blocks_per_rank;
+    const long long base = (long long)k * kBlockElems + threadIdx.x * kElems;
+    const long long ibase = (long long)(k - owner * blocks_per_rank) * kBlockElems + threadIdx.x * kElems;
+    float g[kElems];
+#pragma unroll
+    for (int e = 0; e < kElems; ++e) {
+      const long long i = base + e;
+      float acc = 0.0f;
+      if (i < n) {
+        if (UPDATE) { for (int r = 0; r < n_rows; ++r) acc += rows[(long long)r * row_stride + i]; }
+        else acc = buf[i];
+      }
+      g[e] = acc;
+    }
+    float* dst = inbox(c, owner, seq, c.rank) + ibase;
+#pragma unroll
+    for (int e = 0; e < kElems; ++e) if (base + e < n) dst[e] = g[e];
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) { delay(c); st_release_sys(flags_ar(c, owner, c.rank, k), seq); }
+    if (owner == c.rank) {
+      if (threadIdx.x < c.world) wait_flag(c, flags_ar(c, c.rank, threadIdx.x, k), seq, threadIdx.x);
+      __syncthreads();
+      float out[kElems];
+#pragma unroll
+      for (int e = 0; e < kElems; ++e) {
+        const long long i = base + e;
+        float sum = 0.0f;
+        if (i < n) {
+          for (int s = 0; s < c.world; ++s) sum += __ldcg(inbox(c, c.rank, seq, s) + ibase + e);
+          if (UPDATE) {
+            float p = buf[i];
+            float m = exp_avg ? exp_avg[i] : 0.0f;
+            float v = exp_avg_sq ? exp_avg_sq[i] : 0.0f;
+            apply_update(o, sum * o.grad_scale, p, m, v);
+            if (exp_avg) exp_avg[i] = m;
+            if (exp_avg_sq) exp_avg_sq[i] = v;
+            sum = p;
+          } else {
+            sum *= scale;
+          }
+        }
+        out[e] = sum;
+      }
+      for (int p = 0; p < c.world; ++p) {   // all-gather by peer stores (self included)
+        float* pd = reinterpret_cast<float*>(c.base[p] + c.off_heap + buf_heap_off);
+#pragma unroll
+        for (int e = 0; e < kElems; ++e) if (base + e < n) pd[base + e] = out[e];
+      }
+      __threadfence_system();
+      __syncthreads();
+      if (threadIdx.x == 0)
+        for (int p = 0; p < c.world; ++p) st_release_sys(flags_pr(c, p, k), seq);
+    }
+  }
+  // do not retire before every block of the vector has arrived from its owner
+  for (int k = blockIdx.x; k < n_blocks; k += gridDim.x) {
+    const int owner = k / blocks_per_rank;
+    if (owner != c.rank && threadIdx.x == 0) wait_flag(c, flags_pr(c, c.rank, k), seq, owner);
+  }
+}
+
+// K8 broadcast on the symmetric heap: root copies its bytes into every peer's heap, then flags.
+__global__ void __launch_bounds__(kThreads) broadcast_kernel(Ctx c, uint32_t seq, long long heap_off, long long n16,
+                                                              long long tail_bytes, int root) {
+  uint32_t* bar_local = reinterpret_cast<uint32_t*>(c.base[c.rank] + c.off_flags_bar);
+  if (c.rank == root) {
+    const int4* src = reinterpret_cast<const int4*>(c.base[root] + c.off_heap + heap_off);
+    for (int p = 0; p < c.world; ++p) {
+      if (p == root) continue;
+      int4* dst = reinterpret_cast<int4*>(c.base[p] + c.off_heap + heap_off);
+      for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n16; i += (long long)gridDim.x * kThreads)
+        dst[i] = src[i];
+      if (blockIdx.x == 0 && threadIdx.x < tail_bytes) {
+        const char* s8 = reinterpret_cast<const char*>(src + n16);
+        reinterpret_cast<char*>(dst + n16)[threadIdx.x] = s8[threadIdx.x];
+      }
+    }
+    __threadfence_system();
+    __syncthreads();
+    // count finished CTAs in the root's own slot; the last one publishes to the peers
+    __shared__ unsigned int last;
+    if (threadIdx.x == 0) {
+      unsigned int* cnt = reinterpret_cast<unsigned int*>(bar_local + 2 * B200RNN_MAX_PEERS);
+      const unsigned int done = atomicAdd(cnt, 1u) + 1;
+      last = (done == gridDim.x) ? 1u : 0u;
+      if (last) *cnt = 0;
+    }
+    __syncthreads();
+    if (last && threadIdx.x == 0) {
+      __threadfence_system();
+      delay(c);
+      for (int p = 0; p < c.world; ++p)
+        if (p != root) st_release_sys(reinterpret_cast<uint32_t*>(c.base[p] + c.off_flags_bar) + B200RNN_MAX_PEERS + root, seq);
+    }
+  } else if (blockIdx.x == 0 && threadIdx.x == 0) {
+    wait_flag(c, bar_local + B200RNN_MAX_PEERS + root, seq, root);
+  }
+}
+
+// K9 put + signal / wait.
+__global__ void __launch_bounds__(kThreads) put_kernel(Ctx c, uint32_t seq, int dst, const char* __restrict__ src,
+                                                        long long heap_off, long long bytes) {
+  char* d = c.base[dst] + c.off_heap + heap_off;
+  if (((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(d)) & 15) == 0) {
+    const long long n16 = bytes / 16;
+    for (long long i = threadIdx.x; i < n16; i += kThreads) reinterpret_cast<int4*>(d)[i] = reinterpret_cast<const int4*>(src)[i];
+    for (long long i = n16 * 16 + threadIdx.x; i < bytes; i += kThreads) d[i] = src[i];
+  } else {
+    for (long long i = threadIdx.x; i < bytes; i += kThreads) d[i] = src[i];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    delay(c);
+    st_release_sys(reinterpret_cast<uint32_t*>(c.base[dst] + c.off_flags_sig) + c.rank, seq);
+  }
+}
+__global__ void wait_kernel(Ctx c, uint32_t seq, int src) {
+  if (threadIdx.x == 0) wait_flag(c, reinterpret_cast<uint32_t*>(c.base[c.rank] + c.off_flags_sig) + src, seq, src);
+}
+
+__global__ void barrier_kernel(Ctx c, uint32_t seq) {
+  if (threadIdx.x < c.world) {
+    __threadfence_system();
+    st_release_sys(reinterpret_cast<uint32_t*>(c.base[threadIdx.x] + c.off_flags_bar) + c.rank, seq);
+    wait_flag(c, reinterpret_cast<uint32_t*>(c.base[c.rank] + c.off_flags_bar) + threadIdx.x, seq, threadIdx.x);
+  }
+}
+
+int check_ctx(const b200rnn_comm_ctx* c, const char* who) {
+  B200_REQUIRE(c != nullptr, B200RNN_EINVAL, "%s: null context", who);
+  B200_REQUIRE(c->world >= 1 && c->world <= B200RNN_MAX_PEERS && c->rank >= 0 && c->rank < c->world, B200RNN_EINVAL,
+               "%s: bad rank/world %d/%d", who, c->rank, c->world);
+  for (int i = 0; i < c->world; ++i)
+    B200_REQUIRE(c->base[i] != nullptr, B200RNN_EINVAL, "%s: region of rank %d is not mapped", who, i);
+  return B200RNN_OK;
+}
+
+}  // namespace
+}  // namespace b200rnn
+
+using namespace b200rnn;
+
+extern "C" int64_t b200rnn_comm_layout(b200rnn_comm_ctx* ctx) {
+  if (!ctx || ctx->world < 1 || ctx->world > B200RNN_MAX_PEERS || ctx->max_blocks < 1 || ctx->inbox_floats < 1) return -1;
+  auto align = [](int64_t x) { return (x + 255) & ~int64_t(255); };
+  int64_t off = 0;
+  ctx->off_flags_ar = off;  off = align(off + (int64_t)ctx->world * ctx->max_blocks * 4);
+  ctx->off_flags_pr = off;  off = align(off + (int64_t)ctx->max_blocks * 4);
+  ctx->off_flags_sig = off; off = align(off + B200RNN_MAX_PEERS * 4);
+  ctx->off_flags_bar = off; off = align(off + (2 * B200RNN_MAX_PEERS + 4) * 4);   // barrier | bcast | counter
+  ctx->off_status = off;    off = align(off + 64);
+  ctx->off_inbox = off;     off = align(off + 2 * (int64_t)ctx->world * ctx->inbox_floats * 4);
+  ctx->off_heap = off;      off = align(off + ctx->heap_bytes);
+  return off;
+}
+
+static int launch_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, const float* rows, int n_rows, int64_t n,
+                            float* buf, int64_t heap_off, float* m, float* v, const b200rnn_optim_desc* opt,
+                            float scale, float* metrics, int algo, bool update, cudaStream_t s) {
+  const Ctx c = to_dev(ctx);
+  OptScalars o{};
+  if (update) o = make_opt_scalars(opt);
+  const int64_t row_stride = n + 2;
+  const int64_t one_blocks = ((update ? n + 2 : n) + kThreads - 1) / kThreads;
+  if (algo == B200RNN_ALGO_AUTO) {
+    // one-shot moves W*n floats per rank but pays a single NVLink latency; two-shot moves
+    // 2(W-1)/W*n but pays two.  Crossover measured by bench/allreduce_sweep.py (profiles/).
+    algo = (n * 4 <= 256 * 1024 || ctx->world == 1) ? B200RNN_ALGO_ONESHOT : B200RNN_ALGO_TWOSHOT;
+  }
+  if (algo == B200RNN_ALGO_ONESHOT) {
+    B200_REQUIRE(one_blocks <= ctx->max_blocks, B200RNN_ETOOBIG, "comm one-shot: %lld blocks exceed max_blocks=%d",
+                 (long long)one_blocks, ctx->max_blocks);
+    B200_REQUIRE(n <= ctx->inbox_floats, B200RNN_ETOOBIG, "comm one-shot: n=%lld exceeds inbox capacity %lld",
+                 (long long)n, (long long)ctx->inbox_floats);
+    if (update) oneshot_kernel<true><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
+    else oneshot_kernel<false><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
+  } else {
+    const int64_t n_blocks = (n + kBlockElems - 1) / kBlockElems;
+    const int64_t bpr = (n_blocks + ctx->world - 1) / ctx->world;
+    B200_REQUIRE(n_blocks <= ctx->max_blocks, B200RNN_ETOOBIG, "comm two-shot: %lld blocks exceed max_blocks=%d",
+                 (long long)n_blocks, ctx->max_blocks);
+    B200_REQUIRE(bpr * kBlockElems <= ctx->inbox_floats, B200RNN_ETOOBIG,
+                 "comm two-shot: shard of %lld floats exceeds inbox capacity %lld", (long long)(bpr * kBlockElems),
+                 (long long)ctx->inbox_floats);
+    B200_REQUIRE(heap_off >= 0 && heap_off + n * 4 <= ctx->heap_bytes, B200RNN_EINVAL,
+                 "comm two-shot: the vector must live in the symmetric heap (heap_off=%lld)", (long long)heap_off);
+    int grid = (int)(n_blocks < num_sms() ? n_blocks : num_sms());
+    if (update) twoshot_kernel<true><<<grid, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, heap_off, m, v, o, scale, metrics, (int)n_blocks, (int)bpr);
+    else twoshot_kernel<false><<<grid, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, heap_off, m, v, o, scale, metrics, (int)n_blocks, (int)bpr);
+  }
+  B200_CHECK_LAUNCH();
+  return B200RNN_OK;
+}
+
+extern "C" int b200rnn_comm_allreduce_update(const b200rnn_comm_ctx* ctx, uint32_t seq, const float* rows,
+                                             int32_t n_rows, int64_t n_params, float* params,
+                                             int64_t params_heap_off, float* exp_avg, float* exp_avg_sq,
+                                             const b200rnn_optim_desc* opt, float* metrics, int32_t algo, void* stream) {
+  int rc = check_ctx(ctx, "comm_allreduce_update");
+  if (rc) return rc;
+  B200_REQUIRE(rows && params && opt && n_rows >= 1 && n_params > 0, B200RNN_EINVAL, "comm_allreduce_update: bad argument");
+  B200_REQUIRE(opt->kind != 0 || (exp_avg && exp_avg_sq && opt->step >= 1), B200RNN_EINVAL,
+               "comm_allreduce_update: Adam needs exp_avg/exp_avg_sq and step >= 1");
+  return launch_allreduce(ctx, seq, rows, n_rows, n_params, params, params_heap_off, exp_avg, exp_avg_sq, opt, 1.0f,
+                          metrics, algo, true, (cudaStream_t)stream);
+}
+
+extern "C" int b200rnn_comm_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, float* buf, int64_t n, float scale,
+                                      void* stream) {
+  int rc = check_ctx(ctx, "comm_allreduce");
+  if (rc) return rc;
+  B200_REQUIRE(buf && n > 0, B200RNN_EINVAL, "comm_allreduce: bad argument");
+  return launch_allreduce(ctx, seq, nullptr, 0, n, buf, -1, nullptr, nullptr, nullptr, scale, nullptr,
+                          B200RNN_ALGO_ONESHOT, false, (cudaStream_t)stream);
+}
+
+extern "C" int b200rnn_comm_broadcast(const b200rnn_comm_ctx* ctx, uint32_t seq, int64_t heap_off, int64_t bytes,
+                                      int32_t root, void* stream) {
+  int rc = check_ctx(ctx, "comm_broadcast");
+  if (rc) return rc;
+  B200_REQUIRE(heap_off >= 0 && (heap_off & 15) == 0 && bytes > 0 && heap_off + bytes <= ctx->heap_bytes && root >= 0 &&
+               root < ctx->world, B200RNN_EINVAL, "comm_broadcast: bad range/root");
+  if (ctx->world == 1) return B200RNN_OK;
+  const Ctx c = to_dev(ctx);
+  const int64_t n16 = bytes / 16;
+  int grid = 1;
+  if (ctx->rank == root) { grid = (int)((n16 + kThreads - 1) / kThreads); if (grid < 1) grid = 1; if (grid > 64) grid = 64; }
+  broadcast_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(c, seq, heap_off, n16, bytes - n16 * 16, root);
+  B200_CHECK_LAUNCH();
+  return B200RNN_OK;
+}
+
+extern "C" int b200rnn_comm_put(const b200rnn_comm_ctx* ctx, uint32_t seq, int32_t dst, const void* src,
+                                int64_t heap_off, int64_t bytes, void* stream) {
+  int rc = check_ctx(ctx, "comm_put");
+  if (rc) return rc;
+  B200_REQUIRE(src && dst >= 0 && dst < ctx->world && heap_off >= 0 && bytes > 0 && heap_off + bytes <= ctx->heap_bytes,
+               B200RNN_EINVAL, "comm_put: bad argument");
+  put_kernel<<<1, kThreads, 0, (cudaStream_t)stream>>>(to_dev(ctx), seq, dst, (const char*)src, heap_off, bytes);
+  B200_CHECK_LAUNCH();
+  return B200RNN_OK;
+}
+
+extern "C" int b200rnn_comm_wait(const b200rnn_comm_ctx* ctx, uint32_t seq, int32_t src, void* stream) {
+  int rc = check_ctx(ctx, "comm_wait");
+  if (rc) return rc;
+  B200_REQUIRE(src >= 0 && src < ctx->world, B200RNN_EINVAL, "comm_wait: bad source rank");
+  wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(to_dev(ctx), seq, src);
+  B200_CHECK_LAUNCH();
+  return B200RNN_OK;
+}
+
+extern "C" int b200rnn_comm_barrier(const b200rnn_comm_ctx* ctx, uint32_t seq, void* stream) {
+  int rc = check_ctx(ctx, "comm_barrier");
+  if (rc) return rc;
+  barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(to_dev(ctx), seq);
+  B200_CHECK_LAUNCH();
+  return B200RNN_OK;
+}
+
+extern "C" int b200rnn_comm_status(const b200rnn_comm_ctx* ctx, int32_t* status, void* stream) {
+  int rc = check_ctx(ctx, "comm_status");
+  if (rc) return rc;
+  B200_REQUIRE(status != nullptr, B200RNN_EINVAL, "comm_status: null output");
+  B200_CHECK_CUDA(cudaMemcpyAsync(status, (char*)ctx->base[ctx->rank] + ctx->off_status, 4, cudaMemcpyDeviceToHost,
+                                  (cudaStream_t)stream));
+  B200_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return B200RNN_OK;
+}

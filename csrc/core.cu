@@ -1,6 +1,7 @@
 // Error plumbing + the small memory-bound kernels: K11 dataset gather, K5 head
 // (standalone form), deterministic row reduction, K6 fused optimizer, L2 flush.
 #include "common.cuh"
+#include "optim.cuh"
 #include <math.h>
 
 namespace b200rnn {
@@ -46,26 +47,6 @@ __global__ void reduce_rows_kernel(const float* __restrict__ rows, int n_rows, i
 }
 
 // ---- K6 fused optimizer (W = 1 form; the multi-GPU form lives in comm/) ----
-struct OptScalars {
-  float lr, beta1, beta2, eps, wd, momentum, grad_scale;
-  float step_size, inv_sqrt_bc2;  // Adam bias corrections, computed in double on the host
-  int kind;
-};
-
-__device__ __forceinline__ void apply_update(const OptScalars& o, float g, float& p, float& m, float& v) {
-  if (o.kind == 0) {  // Adam (torch.optim.Adam defaults: no amsgrad, L2 weight decay folded in grad)
-    if (o.wd != 0.0f) g = fmaf(o.wd, p, g);
-    m = fmaf(o.beta1, m, (1.0f - o.beta1) * g);
-    v = fmaf(o.beta2, v, (1.0f - o.beta2) * g * g);
-    const float denom = sqrtf(v) * o.inv_sqrt_bc2 + o.eps;
-    p -= o.step_size * (m / denom);
-  } else {            // SGD (+ optional momentum, torch semantics: buf = mu*buf + g)
-    if (o.wd != 0.0f) g = fmaf(o.wd, p, g);
-    if (o.momentum != 0.0f) { m = fmaf(o.momentum, m, g); g = m; }
-    p -= o.lr * g;
-  }
-}
-
 __global__ void fused_update_kernel(const float* __restrict__ rows, int n_rows, int64_t n_params,
                                     float* __restrict__ params, float* __restrict__ exp_avg,
                                     float* __restrict__ exp_avg_sq, OptScalars o,
@@ -178,23 +159,6 @@ extern "C" int b200rnn_reduce_rows(const float* rows, int32_t n_rows, int64_t ro
   return B200RNN_OK;
 }
 
-namespace b200rnn {
-// shared with comm/: host-side computation of the optimizer scalars
-void fill_opt_scalars(const b200rnn_optim_desc* opt, float* lr, float* b1, float* b2, float* eps, float* wd,
-                      float* mom, float* gs, float* step_size, float* inv_sqrt_bc2, int* kind) {
-  *lr = opt->lr; *b1 = opt->beta1; *b2 = opt->beta2; *eps = opt->eps; *wd = opt->weight_decay;
-  *mom = opt->momentum; *gs = opt->grad_scale; *kind = opt->kind;
-  if (opt->kind == 0) {
-    const double bc1 = 1.0 - pow((double)opt->beta1, (double)opt->step);
-    const double bc2 = 1.0 - pow((double)opt->beta2, (double)opt->step);
-    *step_size = (float)((double)opt->lr / bc1);
-    *inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
-  } else {
-    *step_size = opt->lr; *inv_sqrt_bc2 = 1.0f;
-  }
-}
-}  // namespace b200rnn
-
 extern "C" int b200rnn_fused_update(const float* rows, int32_t n_rows, int64_t n_params, float* params,
                                     float* exp_avg, float* exp_avg_sq, const b200rnn_optim_desc* opt,
                                     float* grad_out, float* metrics, void* stream) {
@@ -204,9 +168,7 @@ extern "C" int b200rnn_fused_update(const float* rows, int32_t n_rows, int64_t n
                "fused_update: Adam needs exp_avg/exp_avg_sq and step >= 1");
   B200_REQUIRE(!(opt->kind == 1 && opt->momentum != 0.0f && !exp_avg), B200RNN_EINVAL,
                "fused_update: SGD momentum needs a momentum buffer (exp_avg)");
-  OptScalars o;
-  fill_opt_scalars(opt, &o.lr, &o.beta1, &o.beta2, &o.eps, &o.wd, &o.momentum, &o.grad_scale,
-                   &o.step_size, &o.inv_sqrt_bc2, &o.kind);
+  const OptScalars o = make_opt_scalars(opt);
   const int threads = 256;
   const int64_t blocks = (n_params + 2 + threads - 1) / threads;
   fused_update_kernel<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(

@@ -164,6 +164,97 @@ int b200rnn_fused_update(const float* rows, int32_t n_rows, int64_t n_params,
 /* ---- L2 flush helper for benchmarking (writes `bytes` of scratch). */
 int b200rnn_l2_flush(void* scratch, int64_t bytes, void* stream);
 
+/* ======================================================================================
+ * Runtime bootstrap + NVLink symmetric memory + in-kernel collectives (csrc/runtime, csrc/comm).
+ * Replaces what the reference gets from mpirun + c10d ProcessGroupMPI + the Horovod core
+ * (src/motion/trainer/ddp.py:18-19, trainer/horovod.py:17,35,41, src/example/example_distributed.py).
+ * ====================================================================================== */
+
+/* ---- B1 rendezvous: star over TCP (rank 0 listens).  Host only, no CUDA. ---- */
+typedef struct b200rnn_boot b200rnn_boot;
+/* rank 0: bind + listen on *port (0 = ephemeral; the chosen port is written back). */
+int b200rnn_boot_listen(int32_t* port, int32_t* listen_fd);
+/* All ranks.  rank 0 passes the fd from b200rnn_boot_listen; others pass -1 and connect to addr:port. */
+int b200rnn_boot_init(int32_t rank, int32_t world, const char* addr, int32_t port, int32_t listen_fd,
+                      int32_t timeout_ms, b200rnn_boot** out);
+int b200rnn_boot_allgather(b200rnn_boot* b, const void* send, int32_t bytes, void* recv /* world*bytes */);
+int b200rnn_boot_barrier(b200rnn_boot* b);
+void b200rnn_boot_destroy(b200rnn_boot* b);
+
+/* ---- B1 topology: what the GPUs of this node can do to each other. ---- */
+typedef struct {
+  int32_t n_devices;
+  int32_t sm_count[B200RNN_MAX_PEERS];
+  int32_t multicast_supported[B200RNN_MAX_PEERS];          /* NVLS (CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED) */
+  int32_t can_access[B200RNN_MAX_PEERS][B200RNN_MAX_PEERS]; /* cudaDeviceCanAccessPeer */
+  int32_t perf_rank[B200RNN_MAX_PEERS][B200RNN_MAX_PEERS];  /* cudaDevP2PAttrPerformanceRank (0 = best) */
+  int32_t native_atomics[B200RNN_MAX_PEERS][B200RNN_MAX_PEERS];
+  char name[B200RNN_MAX_PEERS][64];
+} b200rnn_topology;
+int b200rnn_topology_probe(b200rnn_topology* out);
+
+/* ---- Symmetric memory: one region per rank, every region mapped into every rank.
+ * b200rnn_symm_create ALLOCATES device memory (cudaMalloc + CUDA IPC export/import) and
+ * enables peer access; collective over the bootstrap. ---- */
+typedef struct b200rnn_symm b200rnn_symm;
+int b200rnn_symm_create(b200rnn_boot* b, int32_t device, int64_t bytes, b200rnn_symm** out);
+int b200rnn_symm_pointers(b200rnn_symm* s, void** out /* [world]; out[rank] is the local region */);
+int b200rnn_symm_destroy(b200rnn_symm* s);
+
+/* ---- N7 reducer: bucket assignment in reverse parameter order (c10d policy: 1 MiB first
+ * bucket, then `cap`).  bucket_of[i] = bucket index of parameter i (bucket 0 holds the LAST
+ * parameters, whose gradients are ready first). ---- */
+int b200rnn_bucket_plan(const int64_t* sizes_bytes, int32_t n, int64_t first_cap, int64_t cap,
+                        int32_t* bucket_of, int32_t* n_buckets);
+
+/* ---- Communicator context handed (by value) to every comm kernel. ---- */
+typedef struct {
+  int32_t rank, world;
+  int32_t max_blocks;       /* flag slots per source rank (blocks of the all-reduce) */
+  int32_t delay_ns;         /* injected delay before publishing flags: the analogue of the
+                               reference's tc-netem experiment (fabfile.py:130-191) */
+  int64_t inbox_floats;     /* capacity per (parity, source) inbox */
+  int64_t timeout_cycles;   /* watchdog for flag waits (0 = default) */
+  int64_t heap_bytes;
+  /* byte offsets inside a region (identical on every rank) */
+  int64_t off_flags_ar, off_flags_pr, off_flags_sig, off_flags_bar, off_status, off_inbox, off_heap;
+  void* base[B200RNN_MAX_PEERS];
+} b200rnn_comm_ctx;
+
+/* Fills the off_* fields from world / max_blocks / inbox_floats / heap_bytes; returns region bytes. */
+int64_t b200rnn_comm_layout(b200rnn_comm_ctx* ctx);
+
+enum { B200RNN_ALGO_AUTO = 0, B200RNN_ALGO_ONESHOT = 1, B200RNN_ALGO_TWOSHOT = 2 };
+
+/* K7: ONE kernel = fixed-order reduction of the n_rows local gradient rows + all-reduce over
+ * NVLink peer memory (one-shot: every rank pushes its vector into every peer's inbox; two-shot:
+ * reduce-scatter to the owning rank, optimizer on the owner's shard, all-gather of the updated
+ * PARAMETERS by peer stores) + gradient averaging (opt->grad_scale) + Adam/SGD step.  Ranks sum
+ * in rank order 0..W-1, so all ranks end bit-identical.  For two-shot `params` must live in the
+ * symmetric heap at heap offset params_heap_off.  metrics[2] (nullable) gets this rank's
+ * (loss sum, correct count) from the row tail.  seq must increase by 1 per call on all ranks. */
+int b200rnn_comm_allreduce_update(const b200rnn_comm_ctx* ctx, uint32_t seq, const float* rows,
+                                  int32_t n_rows, int64_t n_params, float* params,
+                                  int64_t params_heap_off, float* exp_avg, float* exp_avg_sq,
+                                  const b200rnn_optim_desc* opt, float* metrics, int32_t algo,
+                                  void* stream);
+/* Plain in-place all-reduce (sum * scale) of buf[n] (n <= inbox_floats), same kernels without
+ * the optimizer epilogue.  Shares the seq counter with b200rnn_comm_allreduce_update. */
+int b200rnn_comm_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, float* buf, int64_t n,
+                           float scale, void* stream);
+/* K8: broadcast `bytes` at heap offset `heap_off` from root's heap into every rank's heap. */
+int b200rnn_comm_broadcast(const b200rnn_comm_ctx* ctx, uint32_t seq, int64_t heap_off, int64_t bytes,
+                           int32_t root, void* stream);
+/* K9: one-sided put of src[bytes] into dst's heap at heap_off, then signal; wait for a signal. */
+int b200rnn_comm_put(const b200rnn_comm_ctx* ctx, uint32_t seq, int32_t dst, const void* src,
+                     int64_t heap_off, int64_t bytes, void* stream);
+int b200rnn_comm_wait(const b200rnn_comm_ctx* ctx, uint32_t seq, int32_t src, void* stream);
+/* Device-side barrier across all ranks. */
+int b200rnn_comm_barrier(const b200rnn_comm_ctx* ctx, uint32_t seq, void* stream);
+/* Reads this rank's watchdog status word (synchronises the stream): 0 = ok, else a bit mask of
+ * (1 << source rank) whose flag never arrived. */
+int b200rnn_comm_status(const b200rnn_comm_ctx* ctx, int32_t* status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,6 +43,28 @@ class OptimDesc(C.Structure):
     ]
 
 
+class CommCtx(C.Structure):
+    _fields_ = [
+        ("rank", C.c_int32), ("world", C.c_int32), ("max_blocks", C.c_int32), ("delay_ns", C.c_int32),
+        ("inbox_floats", C.c_int64), ("timeout_cycles", C.c_int64), ("heap_bytes", C.c_int64),
+        ("off_flags_ar", C.c_int64), ("off_flags_pr", C.c_int64), ("off_flags_sig", C.c_int64),
+        ("off_flags_bar", C.c_int64), ("off_status", C.c_int64), ("off_inbox", C.c_int64), ("off_heap", C.c_int64),
+        ("base", C.c_void_p * MAX_PEERS),
+    ]
+
+
+class Topology(C.Structure):
+    _fields_ = [
+        ("n_devices", C.c_int32),
+        ("sm_count", C.c_int32 * MAX_PEERS),
+        ("multicast_supported", C.c_int32 * MAX_PEERS),
+        ("can_access", (C.c_int32 * MAX_PEERS) * MAX_PEERS),
+        ("perf_rank", (C.c_int32 * MAX_PEERS) * MAX_PEERS),
+        ("native_atomics", (C.c_int32 * MAX_PEERS) * MAX_PEERS),
+        ("name", (C.c_char * 64) * MAX_PEERS),
+    ]
+
+
 class NativeError(RuntimeError):
     pass
 
@@ -66,6 +88,26 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_head_fwd": (i32, [vp, i64, vp, vp, vp, i32, i32, i32, vp, vp, vp]),
         "b200rnn_fused_update": (i32, [vp, i32, i64, vp, vp, vp, P(OptimDesc), vp, vp, vp]),
         "b200rnn_l2_flush": (i32, [vp, i64, vp]),
+        # runtime bootstrap / symmetric memory / reducer
+        "b200rnn_boot_listen": (i32, [P(i32), P(i32)]),
+        "b200rnn_boot_init": (i32, [i32, i32, C.c_char_p, i32, i32, i32, P(vp)]),
+        "b200rnn_boot_allgather": (i32, [vp, vp, i32, vp]),
+        "b200rnn_boot_barrier": (i32, [vp]),
+        "b200rnn_boot_destroy": (None, [vp]),
+        "b200rnn_topology_probe": (i32, [P(Topology)]),
+        "b200rnn_symm_create": (i32, [vp, i32, i64, P(vp)]),
+        "b200rnn_symm_pointers": (i32, [vp, P(vp)]),
+        "b200rnn_symm_destroy": (i32, [vp]),
+        "b200rnn_bucket_plan": (i32, [P(i64), i32, i64, i64, P(i32), P(i32)]),
+        # in-kernel collectives
+        "b200rnn_comm_layout": (i64, [P(CommCtx)]),
+        "b200rnn_comm_allreduce_update": (i32, [P(CommCtx), C.c_uint32, vp, i32, i64, vp, i64, vp, vp, P(OptimDesc), vp, i32, vp]),
+        "b200rnn_comm_allreduce": (i32, [P(CommCtx), C.c_uint32, vp, i64, f32, vp]),
+        "b200rnn_comm_broadcast": (i32, [P(CommCtx), C.c_uint32, i64, i64, i32, vp]),
+        "b200rnn_comm_put": (i32, [P(CommCtx), C.c_uint32, i32, vp, i64, i64, vp]),
+        "b200rnn_comm_wait": (i32, [P(CommCtx), C.c_uint32, i32, vp]),
+        "b200rnn_comm_barrier": (i32, [P(CommCtx), C.c_uint32, vp]),
+        "b200rnn_comm_status": (i32, [P(CommCtx), P(i32), vp]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)

@@ -1,0 +1,125 @@
+"""In-kernel collectives: world-of-one checks on a single GPU, real multi-rank checks on >= 2 GPUs."""
+import copy
+import json
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+from pytorch_distributed_rnn_b200 import FusedAdam
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+@pytest.fixture(scope="module")
+def comm1():
+    from pytorch_distributed_rnn_b200.parallel import process_group as pg
+    from pytorch_distributed_rnn_b200.parallel.symm import SymmComm
+    info = pg.init_distributed()
+    if info.world_size != 1:
+        pytest.skip("single-process fixture")
+    c = SymmComm(info, inbox_floats=1 << 20, heap_bytes=64 << 20)
+    yield c
+    c.close()
+    pg.shutdown()
+
+
+@pytest.mark.gpu
+def test_topology_probe():
+    from pytorch_distributed_rnn_b200.parallel.bootstrap import probe_topology
+    t = probe_topology()
+    assert t["n_devices"] == torch.cuda.device_count() and "B200" in t["names"][0] or t["n_devices"] >= 1
+    assert t["sm_count"][0] > 0 and t["can_access"][0][0] == 1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("algo", [1, 2])
+def test_world1_allreduce_update_equals_fused_update(comm1, algo):
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(129, 65).cuda()
+    ref = copy.deepcopy(lin)
+    arena = comm1.make_arena(lin)
+    opt = FusedAdam(arena, lr=0.01)
+    ropt = torch.optim.Adam(ref.parameters(), lr=0.01)
+    P = arena.numel
+    comm1.algo = algo
+    for step in range(3):
+        rows = torch.randn(5, P + 2, device="cuda")
+        opt.step_count += 1
+        slot = torch.zeros(2, device="cuda")
+        comm1.allreduce_update(rows, 5, arena, opt, opt.desc(grad_scale=1.0), slot)
+        g = rows[:, :P].sum(0)
+        off = 0
+        for p in ref.parameters():
+            p.grad = g[off:off + p.numel()].view_as(p).clone()
+            off += p.numel()
+        ropt.step()
+        assert torch.allclose(slot, rows[:, P:].sum(0), rtol=1e-5)
+    comm1.algo = 0
+    comm1.check()
+    assert torch.allclose(arena.flat[:P], torch.cat([p.detach().view(-1) for p in ref.parameters()]), atol=2e-6)
+
+
+@pytest.mark.gpu
+def test_world1_allreduce_broadcast_barrier(comm1):
+    v = torch.randn(300000, device="cuda")
+    w = v.clone()
+    comm1.allreduce_flat(v, average=True)
+    comm1.barrier()
+    comm1.broadcast_flat(v, root=0)
+    comm1.check()
+    assert torch.equal(v, w)
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_multirank_collectives_and_dp_invariance():
+    from pytorch_distributed_rnn_b200.parallel.launch import launch
+    n = min(torch.cuda.device_count(), 8)
+    res = launch([sys.executable, str(ROOT / "tests" / "multigpu_worker.py")], n, timeout=600)
+    for r, cp in enumerate(res):
+        assert cp.returncode == 0, f"rank {r}:\n{cp.stdout[-3000:]}\n{cp.stderr[-3000:]}"
+        line = [l for l in cp.stdout.splitlines() if l.startswith("RESULT ")][-1]
+        out = json.loads(line[7:])
+        for k, v in out.items():
+            if k.endswith("_ok"):
+                assert v is True, (r, out)
+
+
+def test_bucket_plan_native_matches_python():
+    import ctypes as C
+    from pytorch_distributed_rnn_b200 import _native
+    from pytorch_distributed_rnn_b200.parallel.ddp import plan_buckets
+    lib = _native.load()
+    if lib is None:
+        pytest.skip("native library not built")
+    sizes = [4 * n for n in (1152, 4096, 128, 128, 4096, 4096, 128, 128, 192, 6, 300000, 7000000, 50)]
+    arr = (C.c_int64 * len(sizes))(*sizes)
+    out = (C.c_int32 * len(sizes))()
+    nb = C.c_int32()
+    assert lib.b200rnn_bucket_plan(arr, len(sizes), 1 << 20, 25 << 20, out, C.byref(nb)) == 0
+    py = plan_buckets(sizes)
+    assert nb.value == len(py)
+    for b, ids in enumerate(py):
+        assert all(out[i] == b for i in ids)
+
+
+def test_native_bootstrap_two_processes():
+    import subprocess
+    import textwrap
+    from pytorch_distributed_rnn_b200 import _native
+    from pytorch_distributed_rnn_b200.parallel.launch import free_port
+    if _native.load() is None:
+        pytest.skip("native library not built")
+    port = free_port()
+    code = textwrap.dedent(f'''
+        import sys
+        sys.path.insert(0, {str(ROOT)!r})
+        from pytorch_distributed_rnn_b200.parallel.bootstrap import NativeBootstrap
+        r = int(sys.argv[1]); b = NativeBootstrap(r, 2, "127.0.0.1", {port}, timeout_ms=30000)
+        out = b.allgather(b"rank%d" % r); b.barrier(); print(b"|".join(out).decode()); b.close()
+    ''')
+    ps = [subprocess.Popen([sys.executable, "-c", code, str(r)], stdout=subprocess.PIPE, text=True) for r in range(2)]
+    outs = [p.communicate(timeout=90)[0].strip() for p in ps]
+    assert outs == ["rank0|rank1", "rank0|rank1"]
