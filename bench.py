@@ -37,6 +37,8 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
+# stdout carries exactly ONE JSON line: send NCCL's own log lines (e.g. "NCCL version ...") to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 GLOBAL_BATCH, SEQ_LEN, FEATURES, HIDDEN, LAYERS, CLASSES, TRAIN_SIZE = 1440, 128, 9, 32, 2, 6, 6912
 LR, SEED = 0.0025, 123456789
