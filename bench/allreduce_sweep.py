@@ -1,0 +1,120 @@
+#!/usr/bin/env python
+"""Gradient all-reduce latency / bandwidth sweep, 4 KB - 256 MB, in-kernel NVLink vs NCCL.
+
+This is the analogue of the reference's network experiment (fabfile.py:130-191,
+evaluation/Experiments_network.ipynb): there, `tc netem` delay/loss was injected on 12 Pis and
+the epoch time of DDP vs Horovod was recorded; here the interconnect is NVLink 5 / NVSwitch, so
+the experiment becomes (a) the latency/bandwidth curve of the gradient all-reduce itself for each
+algorithm (one-shot / two-shot / NCCL) and (b) the same curve with an injected delay in front of
+every flag publication (``--delay-us``), which shows how each algorithm's critical path multiplies
+a per-message latency (one-shot: x1, two-shot: x2 — cf. DDP's ~25 serialized latencies per step and
+Horovod's extra negotiation rounds).
+
+Launch (N ranks):  torchrun --nproc-per-node N bench/allreduce_sweep.py [--out results.json]
+Timing: CUDA events on the launching stream, per size 20 iterations after 5 warm-ups, max over
+ranks.  Roofline per size: bytes that must cross NVLink per rank / 770 GB/s (measured peer copy
+bandwidth, B200_PROFILING.md); one-shot sends (W-1)*S, two-shot 2*(W-1)/W*S.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from pytorch_distributed_rnn_b200 import FusedSGD, _native  # noqa: E402
+from pytorch_distributed_rnn_b200.parallel import process_group as pg  # noqa: E402
+from pytorch_distributed_rnn_b200.parallel.symm import SymmComm  # noqa: E402
+
+NVLINK_GBS = 770.0
+
+
+def timed(fn, iters, warm, dev):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize(dev)
+    dist.barrier()
+    ts = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record()
+        torch.cuda.synchronize(dev)
+        ts.append(a.elapsed_time(b) * 1e3)
+    t = torch.tensor([sorted(ts)[len(ts) // 2]], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--min-bytes", type=int, default=4 << 10)
+    ap.add_argument("--max-bytes", type=int, default=256 << 20)
+    ap.add_argument("--delay-us", type=str, default="0", help="comma list of injected delays (us)")
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--out", default=None)
+    a = ap.parse_args()
+    info = pg.init_distributed()
+    rank, world, dev = info.rank, info.world_size, info.device
+    max_floats = a.max_bytes // 4
+    comm = SymmComm(info, inbox_floats=max_floats, heap_bytes=a.max_bytes + (64 << 20), max_blocks=1 << 18)
+    lib = _native.lib()
+    results = []
+    sizes = []
+    b = a.min_bytes
+    while b <= a.max_bytes:
+        sizes.append(b)
+        b *= 4
+    for delay in [int(x) for x in a.delay_us.split(",")]:
+        comm.set_delay_ns(delay * 1000)
+        for nbytes in sizes:
+            n = nbytes // 4
+            # the vector lives in the symmetric heap (needed by two-shot's parameter all-gather)
+            lin = torch.nn.Linear(n - 1, 1, bias=True, device=dev) if n > 1 else None
+            arena = comm.make_arena(lin)
+            opt = FusedSGD(arena, lr=0.0)
+            rows = torch.ones(1, n + 2, device=dev)
+            slot = torch.zeros(2, device=dev)
+            row = {"bytes": nbytes, "world": world, "delay_us": delay}
+            for algo, name in ((1, "oneshot"), (2, "twoshot")):
+                if algo == 1 and (n + 255) // 256 > comm.ctx.max_blocks:
+                    continue
+                comm.algo = algo
+
+                def fn():
+                    opt.step_count += 1
+                    comm.allreduce_update(rows, 1, arena, opt, opt.desc(grad_scale=1.0 / world), slot)
+                row[f"{name}_us"] = timed(fn, a.iters, 5, dev)
+            comm.algo = 0
+            if delay == 0:
+                t = torch.ones(n, device=dev)
+                row["nccl_us"] = timed(lambda: dist.all_reduce(t), a.iters, 5, dev)
+            per_rank_one = (world - 1) * nbytes
+            per_rank_two = 2 * (world - 1) / world * nbytes
+            row["roofline_oneshot_us"] = per_rank_one / (NVLINK_GBS * 1e3)
+            row["roofline_twoshot_us"] = per_rank_two / (NVLINK_GBS * 1e3)
+            for name in ("oneshot", "twoshot", "nccl"):
+                if f"{name}_us" in row:
+                    roof = row["roofline_oneshot_us"] if name == "oneshot" else row["roofline_twoshot_us"]
+                    row[f"{name}_frac_of_nvlink_roofline"] = roof / row[f"{name}_us"] if row[f"{name}_us"] > 0 else None
+                    row[f"{name}_busbw_GBs"] = 2 * (world - 1) / world * nbytes / row[f"{name}_us"] / 1e3
+            comm.check()
+            results.append(row)
+            if rank == 0:
+                print(json.dumps(row), flush=True)
+            # free the heap slot of this size (bump allocator: rewind, sizes only grow)
+            comm._heap_top = arena.heap_off
+    if rank == 0 and a.out:
+        Path(a.out).parent.mkdir(parents=True, exist_ok=True)
+        json.dump({"results": results, "nvlink_GBs": NVLINK_GBS,
+                   "note": "fused = reduce 1 local row + all-reduce + SGD(lr=0) epilogue, in one kernel"}, open(a.out, "w"), indent=1)
+    dist.barrier()
+    comm.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,108 @@
+#!/usr/bin/env python
+"""Experiment grid runner — the fabfile analogue (fabfile.py:48-66,194-290).
+
+Grid: batch size {480, 960, 1440} x ranks {1, 2, 4, 8} (one rank per GPU; the reference used
+1/2/4/8/12 Pi hosts) x trainer {local (1 rank only), distributed, horovod}, every run with
+``--epochs 1 --seed 123456789 --no-validation`` like TRAIN_RUNS.  Behaviour kept from
+``run_training``: configurations are shuffled, a command already present in the results file
+is skipped (experiment-level resume), a failed run is recorded rather than aborting the sweep,
+and the file is rewritten after every run in the reference's schema
+``{"results": [{command, stdout, stderr, config{trainer,hosts,slots,parameters}}]}`` so the
+analysis (bench/analysis.py, the notebooks' successor) parses both.  Fixes: the results file is
+created if missing (quirk Q15).  ``--network`` runs the delay-injection variant (O2): the
+``distributed`` and ``horovod`` trainers at the largest rank count for each injected delay.
+
+    python bench/sweep.py --dataset-path /tmp/motion --results results.json [--ranks 1,2,4,8] [--repeats 2]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import random
+import subprocess
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+BATCH_SIZES = [480, 960, 1440]
+TRAINERS = ["local", "distributed", "horovod"]
+DELAYS_US = [0, 1, 2, 5, 10, 25, 50, 100, 200, 300, 400]   # the reference's delay list, ms -> us (NVLink scale)
+
+
+def train_runs(ranks, repeats):
+    return [{"trainer": tr, "hosts": n, "slots": 1, "repeat": rep,
+             "parameters": {"--batch-size": bs, "--epochs": 1, "--seed": 123456789, "--no-validation": ""}}
+            for bs in BATCH_SIZES for n in ranks for tr in TRAINERS for rep in range(repeats)
+            if tr != "local" or n == 1]
+
+
+def get_command(run, dataset_path, extra=()):
+    params = []
+    for k, v in run["parameters"].items():
+        params += [k] if v == "" else [k, str(v)]
+    base = ["--dataset-path", str(dataset_path), "--synthetic", "--deferred-logging", *params, *extra, run["trainer"]]
+    n = run["hosts"] * run["slots"]
+    if run["trainer"] == "local":
+        return [sys.executable, "-m", "pytorch_distributed_rnn_b200", *base]
+    return [sys.executable, "-m", "pytorch_distributed_rnn_b200.parallel.launch", "-n", str(n),
+            "-m", "pytorch_distributed_rnn_b200", *base]
+
+
+def load_results(path):
+    if not Path(path).exists():
+        return []
+    with open(path) as f:
+        return json.load(f)["results"]
+
+
+def run_training(runs, dataset_path, results_file, env=None, tag=None):
+    runs = list(runs)
+    random.shuffle(runs)
+    for i, run in enumerate(runs):
+        cmd = get_command(run, dataset_path)
+        command = " ".join(cmd) + (f"  #{tag}" if tag else "") + f"  #repeat{run.get('repeat', 0)}"
+        results = load_results(results_file)
+        if any(r["command"] == command for r in results):
+            print(f"[{i + 1}/{len(runs)}] skip (already recorded): {command}")
+            continue
+        print(f"[{i + 1}/{len(runs)}] {command}", flush=True)
+        e = dict(os.environ, PYTHONPATH=str(ROOT))
+        e.update(env or {})
+        cp = subprocess.run(cmd, capture_output=True, text=True, env=e, cwd=str(ROOT))  # warn=True semantics
+        entry = {"command": command, "stdout": cp.stdout, "stderr": cp.stderr, "returncode": cp.returncode,
+                 "config": {k: run[k] for k in ("trainer", "hosts", "slots", "parameters")}}
+        if tag:
+            entry.update(tag_fields(tag))
+        results.append(entry)
+        with open(results_file, "w") as f:
+            json.dump({"results": results}, f)
+
+
+def tag_fields(tag):
+    kind, value = tag.split("=")
+    return {"rule_type": kind, "rule_value": float(value), "rule": f"{kind} {value}us"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--dataset-path", default="/tmp/b200rnn_motion")
+    ap.add_argument("--results", default="results.json")
+    ap.add_argument("--ranks", default="1,2,4,8")
+    ap.add_argument("--repeats", type=int, default=2)
+    ap.add_argument("--network", action="store_true", help="delay-injection experiment instead of the scaling grid")
+    a = ap.parse_args()
+    ranks = [int(x) for x in a.ranks.split(",")]
+    if not a.network:
+        run_training(train_runs(ranks, a.repeats), a.dataset_path, a.results)
+        return
+    n = max(ranks)
+    for d in DELAYS_US:
+        runs = [{"trainer": tr, "hosts": n, "slots": 1,
+                 "parameters": {"--batch-size": 1440, "--epochs": 1, "--seed": 123456789, "--no-validation": ""}}
+                for tr in ("distributed", "horovod")]
+        run_training(runs, a.dataset_path, a.results, env={"B200RNN_DELAY_NS": str(d * 1000)}, tag=f"delay={d}")
+
+
+if __name__ == "__main__":
+    main()

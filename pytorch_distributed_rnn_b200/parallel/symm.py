@@ -76,6 +76,7 @@ class SymmComm:
                 boot = NativeBootstrap(0, 1)
         self.boot = boot
         ctx = CommCtx()
+        delay_ns = delay_ns or int(os.environ.get("B200RNN_DELAY_NS", "0"))
         ctx.rank, ctx.world, ctx.max_blocks, ctx.delay_ns = self.rank, self.world, max_blocks, delay_ns
         ctx.inbox_floats, ctx.timeout_cycles, ctx.heap_bytes = inbox_floats, 0, heap_bytes
         region = self.lib.b200rnn_comm_layout(C.byref(ctx))
