@@ -161,6 +161,21 @@ int b200rnn_fused_update(const float* rows, int32_t n_rows, int64_t n_params,
                          const b200rnn_optim_desc* opt, float* grad_out,
                          float* metrics, void* stream);
 
+/* ---- K1/K4: bf16 GEMM on tcgen05 tensor cores (TMA-fed, TMEM accumulators).
+ * C[M,N] (+)= A[M,K] x B[N,K]^T + bias[N]; A, B bf16 row-major (K contiguous, lda/ldb multiples
+ * of 8, 16-byte aligned), C fp32 or bf16 (c_is_bf16), accumulate != 0 adds to the existing C.
+ * Used for the input projection over all timesteps (src/motion/model.py:14), the per-step
+ * recurrent projection at large hidden sizes and the weight-gradient GEMMs (trainer/base.py:116). */
+int b200rnn_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int32_t M, int32_t N,
+                      int32_t K, int32_t lda, int32_t ldb, int32_t ldc, int32_t accumulate,
+                      int32_t c_is_bf16, void* stream);
+/* 0 = no tensor-core pipeline timeout has been observed since the library was loaded. */
+int b200rnn_gemm_status(int32_t* status);
+/* fp32 -> bf16 cast; and cast + transpose [rows, cols] -> [cols, rows]. */
+int b200rnn_cast_bf16(const float* in, void* out, int64_t n, void* stream);
+int b200rnn_transpose_cast_bf16(const float* in, void* out, int32_t rows, int32_t cols, int64_t ld_in,
+                                int64_t ld_out, void* stream);
+
 /* ---- L2 flush helper for benchmarking (writes `bytes` of scratch). */
 int b200rnn_l2_flush(void* scratch, int64_t bytes, void* stream);
 

@@ -88,6 +88,10 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_head_fwd": (i32, [vp, i64, vp, vp, vp, i32, i32, i32, vp, vp, vp]),
         "b200rnn_fused_update": (i32, [vp, i32, i64, vp, vp, vp, P(OptimDesc), vp, vp, vp]),
         "b200rnn_l2_flush": (i32, [vp, i64, vp]),
+        "b200rnn_gemm_bf16": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+        "b200rnn_gemm_status": (i32, [P(i32)]),
+        "b200rnn_cast_bf16": (i32, [vp, vp, i64, vp]),
+        "b200rnn_transpose_cast_bf16": (i32, [vp, vp, i32, i32, i64, i64, vp]),
         # runtime bootstrap / symmetric memory / reducer
         "b200rnn_boot_listen": (i32, [P(i32), P(i32)]),
         "b200rnn_boot_init": (i32, [i32, i32, C.c_char_p, i32, i32, i32, P(vp)]),
