@@ -56,6 +56,16 @@ struct BwdArgs {
   int I, T, B, L, BT, C;
 };
 
+// Column of operand element k inside a staged row: each thread-slice of KPT columns is padded by 4
+// floats when KPT is a multiple of 8, so the KQ lanes of a hidden unit (which read the same row at
+// different slices) hit different banks with their 128-bit loads.
+template <int KPT>
+__device__ __forceinline__ constexpr int vcol(int k) { return (KPT % 8 == 0) ? (k / KPT) * (KPT + 4) + (k % KPT) : k; }
+// Position of gate-gradient element j' (= unit*4 + gate) inside a dG row: the JQ slices read by the
+// B mapping are padded by 4 floats each; rows are DG_LD = 4H + 24 floats apart (== 24 mod 32 banks)
+template <int JR>
+__device__ __forceinline__ constexpr int dgcol(int jp) { return (jp / JR) * (JR + 4) + (jp % JR); }
+
 template <int KQ>
 __device__ __forceinline__ float group_sum(float v) {
 #pragma unroll
@@ -99,7 +109,7 @@ __device__ __forceinline__ void fwd_layer(
   constexpr int KPAD = KQ * KPT;
   constexpr int INP = KPAD - H;           // padded input width of this layer
   constexpr int BTMAX = NG * KQ;
-  constexpr int VS_LD = 2 * H + 4;        // row stride of vs (max KPAD = 2H, +4 de-conflicts banks)
+  constexpr int VS_LD = 2 * H + 4 * KQ + 4;   // row stride of vs (max KPAD = 2H plus slice padding)
   constexpr int NPF = (BTMAX * INP + NT - 1) / NT;
   static_assert(INP > 0 && INP % 4 == 0 && KPT % 4 == 0, "bad K split");
 
@@ -141,15 +151,16 @@ __device__ __forceinline__ void fwd_layer(
     for (int i = 0; i < NPF; ++i) {
       const int idx = tid + i * NT;
       const int b = idx / INP, k = idx % INP;
-      if (idx < BTMAX * INP) vs[(buf * BTMAX + b) * VS_LD + k] = pf[i];
+      if (idx < BTMAX * INP) vs[(buf * BTMAX + b) * VS_LD + vcol<KPT>(k)] = pf[i];
     }
   };
 
   load_inputs(0);
-  store_inputs(0);
   // all rows of both buffers start finite (rows >= BTc are computed but never used)
-  for (int idx = tid; idx < 2 * BTMAX * VS_LD; idx += NT)
-    if ((idx % VS_LD) >= INP || idx >= BTMAX * VS_LD) vs[idx] = 0.0f;
+  __syncthreads();
+  for (int idx = tid; idx < 2 * BTMAX * VS_LD; idx += NT) vs[idx] = 0.0f;
+  __syncthreads();
+  store_inputs(0);
   float c_reg[NG];
 #pragma unroll
   for (int g = 0; g < NG; ++g) c_reg[g] = 0.0f;
@@ -167,7 +178,7 @@ __device__ __forceinline__ void fwd_layer(
       for (int si = 0; si < KQ; ++si) {
         const int b = g * KQ + si;
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-        const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + kq * KPT]);
+        const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + vcol<KPT>(kq * KPT)]);
 #pragma unroll
         for (int j4 = 0; j4 < KPT / 4; ++j4) {
           const float4 v = vp[j4];
@@ -195,7 +206,7 @@ __device__ __forceinline__ void fwd_layer(
         const float c = fmaf(fg, c_reg[g], ig * gg);
         const float h = og * tanh_f(c);
         c_reg[g] = c;
-        vs[(nxt * BTMAX + b) * VS_LD + INP + u] = h;
+        vs[(nxt * BTMAX + b) * VS_LD + vcol<KPT>(INP + u)] = h;
         const int64_t e = ((int64_t)t * B + (b0 + b)) * H + u;
         h_seq[e] = h;
         if (training) {
@@ -213,7 +224,7 @@ template <int H, int KQ, int KPT0, int NG>
 __global__ void __launch_bounds__(H* KQ) lstm_fwd_kernel(const FwdArgs a) {
   constexpr int KPT1 = 2 * H / KQ;
   constexpr int BTMAX = NG * KQ;
-  constexpr int VS_LD = 2 * H + 4;
+  constexpr int VS_LD = 2 * H + 4 * KQ + 4;
   __shared__ __align__(16) float vs[2 * BTMAX * VS_LD];
   const int b0 = blockIdx.x * a.BT;
   const int BTc = min(a.BT, a.B - b0);
@@ -257,7 +268,8 @@ __device__ __forceinline__ void bwd_layer(
   constexpr int KPAD = KQ * KPT;
   constexpr int INP = KPAD - H;
   constexpr int BTMAX = NG * KQ;
-  constexpr int VS_LD = 2 * H + 4;
+  constexpr int VS_LD = 2 * H + 4 * KQ + 4;
+  constexpr int DG_LD = 4 * H + 24;            // dG row stride (floats)
   constexpr int G4 = 4 * H;                    // gate rows
   constexpr int NOUT = HAS_DX ? KPAD : H;      // columns of dG x [W_ih|W_hh] we need
   constexpr int KOFF = HAS_DX ? 0 : INP;
@@ -267,6 +279,12 @@ __device__ __forceinline__ void bwd_layer(
   constexpr int NPFH = (BTMAX * H + NT - 1) / NT;
   static_assert(NT % NOUT == 0 && JQ >= 1 && (JQ & (JQ - 1)) == 0 && JR % 4 == 0, "bad B mapping");
   static_assert(!HAS_DX || INP == H, "dx only for stacked layers (input width == H)");
+
+  // all rows of the staging buffers start at zero: the sample loops below are compile-time (BTMAX
+  // iterations, full ILP) and rows past the tile end must contribute nothing
+  for (int idx = threadIdx.x; idx < 2 * BTMAX * VS_LD; idx += 2 * NT) vs[idx] = 0.0f;
+  for (int idx = threadIdx.x; idx < BTMAX * DG_LD; idx += 2 * NT) dG_s[idx] = 0.0f;
+  __syncthreads();
 
   const bool roleA = threadIdx.x < NT;
   const int tid = roleA ? threadIdx.x : threadIdx.x - NT;   // role-local id
@@ -334,16 +352,16 @@ __device__ __forceinline__ void bwd_layer(
           const float dpo = dh * tc * og * (1.0f - og);
           dc_reg[g] = dct * fg;
           c_t[g] = cprev[g];
-          reinterpret_cast<float4*>(dG_s)[b * H + u] = make_float4(dpi, dpf, dpg, dpo);
+          *reinterpret_cast<float4*>(&dG_s[b * DG_LD + dgcol<JR>(u * 4)]) = make_float4(dpi, dpf, dpg, dpo);
           dbacc[0] += dpi; dbacc[1] += dpf; dbacc[2] += dpg; dbacc[3] += dpo;
         }
       }
       __syncthreads();  // (S1) dG_s complete
       // ---- phase B2: dW += dG^T [x_t | h_{t-1}] ----
-#pragma unroll 2
-      for (int b = 0; b < BTc; ++b) {
-        const float4 d = reinterpret_cast<const float4*>(dG_s)[b * H + u];
-        const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + kq * KPT]);
+#pragma unroll
+      for (int b = 0; b < BTMAX; ++b) {
+        const float4 d = *reinterpret_cast<const float4*>(&dG_s[b * DG_LD + dgcol<JR>(u * 4)]);
+        const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + vcol<KPT>(kq * KPT)]);
 #pragma unroll
         for (int j4 = 0; j4 < KPT / 4; ++j4) {
           const float4 v = vp[j4];
@@ -412,12 +430,12 @@ __device__ __forceinline__ void bwd_layer(
 #pragma unroll
       for (int i = 0; i < NPFX; ++i) {
         const int idx = tid + i * NT;
-        if (idx < BTMAX * INP) vs[(buf * BTMAX + idx / INP) * VS_LD + (idx % INP)] = pfx[i];
+        if (idx < BTMAX * INP) vs[(buf * BTMAX + idx / INP) * VS_LD + vcol<KPT>(idx % INP)] = pfx[i];
       }
 #pragma unroll
       for (int i = 0; i < NPFH; ++i) {
         const int idx = tid + i * NT;
-        if (idx < BTMAX * H) vs[(buf * BTMAX + idx / H) * VS_LD + INP + (idx % H)] = pfh[i];
+        if (idx < BTMAX * H) vs[(buf * BTMAX + idx / H) * VS_LD + vcol<KPT>(INP + (idx % H))] = pfh[i];
       }
     };
     load_operands(T - 1);
@@ -429,21 +447,31 @@ __device__ __forceinline__ void bwd_layer(
       if (t > 0) load_operands(t - 1);   // global loads in flight across the barrier
       __syncthreads();  // (S1) dG_s complete
       // ---- phase B1: dv = dG x [W_ih | W_hh]  (dx for the layer below, dh for step t-1) ----
-#pragma unroll 2
-      for (int b = 0; b < BTc; ++b) {
-        const float4* dp = reinterpret_cast<const float4*>(&dG_s[b * G4 + jq * JR]);
-        float acc0 = 0.0f, acc1 = 0.0f, acc2 = 0.0f, acc3 = 0.0f;  // 4 independent chains per sample
+      // all dot products first (BTMAX x 4 independent FMA chains, loads hoistable), then the
+      // lane reductions back to back, then the stores
+      float res[BTMAX];
+#pragma unroll
+      for (int b = 0; b < BTMAX; ++b) {
+        const float4* dp = reinterpret_cast<const float4*>(&dG_s[b * DG_LD + jq * (JR + 4)]);
+        float acc0 = 0.0f, acc1 = 0.0f, acc2 = 0.0f, acc3 = 0.0f;
 #pragma unroll
         for (int j4 = 0; j4 < JR / 4; ++j4) {
           const float4 d = dp[j4];
           acc0 = fmaf(wt[4 * j4 + 0], d.x, acc0); acc1 = fmaf(wt[4 * j4 + 1], d.y, acc1);
           acc2 = fmaf(wt[4 * j4 + 2], d.z, acc2); acc3 = fmaf(wt[4 * j4 + 3], d.w, acc3);
         }
-        const float acc = group_sum<JQ>((acc0 + acc1) + (acc2 + acc3));
-        if (jq == 0) {
-          const int kk = KOFF + kB;
-          if (HAS_DX && kk < INP) dx_out[((int64_t)t * B + (b0 + b)) * H + kk] = acc;
-          else dhrec_s[b * H + (kk - INP)] = acc;
+        res[b] = (acc0 + acc1) + (acc2 + acc3);
+      }
+#pragma unroll
+      for (int b = 0; b < BTMAX; ++b) res[b] = group_sum<JQ>(res[b]);
+      if (jq == 0) {
+        const int kk = KOFF + kB;
+#pragma unroll
+        for (int b = 0; b < BTMAX; ++b) {
+          if (b < BTc) {
+            if (HAS_DX && kk < INP) dx_out[((int64_t)t * B + (b0 + b)) * H + kk] = res[b];
+            else dhrec_s[b * H + (kk - INP)] = res[b];
+          }
         }
       }
       if (t > 0) store_operands(nxt);
@@ -453,14 +481,15 @@ __device__ __forceinline__ void bwd_layer(
 }
 
 template <int H, int KQ, int KPT0, int NG>
-__global__ void __launch_bounds__(2 * H * KQ, 2) lstm_bwd_kernel(const BwdArgs a) {
+__global__ void __launch_bounds__(2 * H * KQ, 1) lstm_bwd_kernel(const BwdArgs a) {
   constexpr int NT2 = 2 * H * KQ;   // all threads (both roles)
   constexpr int KPT1 = 2 * H / KQ;
   constexpr int BTMAX = NG * KQ;
-  constexpr int VS_LD = 2 * H + 4;
+  constexpr int VS_LD = 2 * H + 4 * KQ + 4;
+  constexpr int DG_LD = 4 * H + 24;
   constexpr int CMAX = 32;
   __shared__ __align__(16) float vs[2 * BTMAX * VS_LD];
-  __shared__ __align__(16) float dG_s[BTMAX * 4 * H];
+  __shared__ __align__(16) float dG_s[BTMAX * DG_LD];
   __shared__ __align__(16) float dhrec_s[BTMAX * H];
   __shared__ float lg_s[BTMAX * CMAX];   // logits, then dlogits
 
@@ -594,13 +623,17 @@ int choose_bt_fwd(int B) {
   }
   return best;
 }
-// Backward loops over samples with a runtime bound, so any tile size works: two CTAs per SM
-// (its register budget), i.e. 4 warps per scheduler.
+// Backward: the sample loops are compile-time over the tile (multiples of KQ), one CTA of 8 warps
+// per SM (its register budget): minimise the per-SM load like the forward does.
 int choose_bt(int B) {
-  int bt = (B + 2 * num_sms() - 1) / (2 * num_sms());
-  if (bt < 1) bt = 1;
-  if (bt > kMaxBT) bt = kMaxBT;
-  return bt;
+  const int sms = num_sms();
+  int best = 4, best_load = 1 << 30;
+  for (int bt = 4; bt <= kMaxBT; bt += 4) {
+    const int n = (B + bt - 1) / bt;
+    const int load = ((n + sms - 1) / sms) * bt;
+    if (load <= best_load) { best_load = load; best = bt; }   // ties: larger tile = a single wave
+  }
+  return best;
 }
 
 bool small_supported(const b200rnn_model_desc* d) {

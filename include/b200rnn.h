@@ -88,6 +88,15 @@ int64_t b200rnn_grad_row_floats(const b200rnn_model_desc* d);
 int b200rnn_lstm_fwd(const b200rnn_model_desc* d, const float* params,
                      const float* x, float* stash, int32_t training, void* stream);
 
+/* Tensor-core form of b200rnn_lstm_fwd (same arguments, same stash): the per-step gate
+ * pre-activations of a batch tile are one tcgen05.mma GEMM (M=128 gate rows, N=16 samples,
+ * kind::tf32, 3xTF32 split for fp32 fidelity) with [W_ih|W_hh] resident in shared memory and the
+ * accumulator in TMEM (csrc/rnn/lstm_tc.cu). */
+int b200rnn_lstm_fwd_tc(const b200rnn_model_desc* d, const float* params,
+                        const float* x, float* stash, int32_t training, void* stream);
+/* 0 = no tensor-core recurrent kernel has hit its mbarrier watchdog since load. */
+int b200rnn_tc_status(int32_t* status);
+
 /* Backward through time for all layers.  Gradient sources (all optional):
  *   labels != NULL && d->num_classes > 0: the classifier head + mean
  *       cross-entropy + correct-count are evaluated in-kernel on

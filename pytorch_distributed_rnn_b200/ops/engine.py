@@ -18,6 +18,7 @@ buffer that the trainer reads when it wants to log.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, Optional, Tuple
 
 import torch
@@ -39,6 +40,11 @@ class FusedTrainEngine:
         if not p0.is_cuda:
             raise ValueError("FusedTrainEngine needs the model on a CUDA device")
         self.lib = _native.lib()
+        # forward engine: "ffma" = CUDA-core persistent kernel (default: fastest at H=32, where the
+        # recurrence is bound by the serial chain and a tcgen05.mma costs ~64 cycles to issue
+        # whatever its N — see DESIGN.md), "tc" = tcgen05/TMEM recurrent kernel (3xTF32)
+        self.fwd_kind = os.environ.get("B200RNN_FWD", "ffma")
+        self._fwd = self.lib.b200rnn_lstm_fwd_tc if self.fwd_kind == "tc" else self.lib.b200rnn_lstm_fwd
         self.model = model
         self.device = p0.device
         self.comm = comm
@@ -98,7 +104,7 @@ class FusedTrainEngine:
         y = y.reshape(-1)
         sp = _native.stream_ptr(self.device)
         a, opt = self.arena, self.optimizer
-        _native.check(self.lib.b200rnn_lstm_fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 1, sp), "lstm_fwd")
+        _native.check(self._fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 1, sp), "lstm_fwd")
         _native.check(self.lib.b200rnn_lstm_bwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(),
                                                 y.data_ptr(), 1.0 / B, None, None, None, buf["scratch"].data_ptr(), sp), "lstm_bwd")
         opt.step_count += 1
@@ -156,7 +162,7 @@ class FusedTrainEngine:
         sp = _native.stream_ptr(self.device)
         a, m = self.arena, self.model
         H, L = m.hidden_dim, m.layer_dim
-        _native.check(self.lib.b200rnn_lstm_fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 0, sp), "lstm_fwd")
+        _native.check(self._fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 0, sp), "lstm_fwd")
         h_last = buf["stash"][((L - 1) * T + (T - 1)) * B * H:][:B * H]
         _native.check(self.lib.b200rnn_head_fwd(h_last.data_ptr(), H, m.fc.weight.data_ptr(), m.fc.bias.data_ptr(),
                                                 y.data_ptr(), B, H, m.output_dim, None, self.eval_metrics.data_ptr(), sp), "head_fwd")

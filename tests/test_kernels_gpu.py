@@ -143,3 +143,32 @@ def test_unsupported_shape_falls_back_to_composite_and_is_correct():
     x = torch.randn(4, 6, 9)
     out, _ = m(x.to(DEV))
     assert torch.allclose(out.detach().cpu(), ref(x)[0], atol=1e-4)
+
+
+@pytest.mark.parametrize("B,T,I,L", [(5, 7, 9, 1), (37, 16, 9, 2), (1440, 128, 9, 2), (33, 12, 20, 3), (300, 5, 32, 2)])
+def test_tensor_core_forward_matches_torch_and_ffma(B, T, I, L):
+    """tcgen05 recurrent kernel (3xTF32) against stock fp32 nn.LSTM and against the FFMA kernel's stash."""
+    from pytorch_distributed_rnn_b200.ops.rnn_function import canonical_desc, packed_params
+    lib = _native.lib()
+    torch.manual_seed(B * 3 + T)
+    m = FusedLSTM(I, 32, L, batch_first=True).to(DEV)
+    ref = _stock_lstm(m)
+    x = torch.randn(B, T, I)
+    xd = x.to(DEV)
+    d = canonical_desc("lstm", I, 32, L, B, T, 0)
+    params = packed_params(m.flat_weights())
+    n = lib.b200rnn_rnn_stash_floats(C.byref(d))
+    s_tc = torch.zeros(n, device=DEV)
+    s_ff = torch.zeros(n, device=DEV)
+    sp = _native.stream_ptr()
+    _native.check(lib.b200rnn_lstm_fwd_tc(C.byref(d), params.data_ptr(), xd.data_ptr(), s_tc.data_ptr(), 1, sp), "fwd_tc")
+    _native.check(lib.b200rnn_lstm_fwd(C.byref(d), params.data_ptr(), xd.data_ptr(), s_ff.data_ptr(), 1, sp), "fwd")
+    torch.cuda.synchronize()
+    st = C.c_int32(-1)
+    _native.check(lib.b200rnn_tc_status(C.byref(st)))
+    assert st.value == 0, "tensor-core pipeline watchdog fired"
+    with torch.no_grad():
+        ro, _ = ref(x)
+    out_tc = s_tc[:L * T * B * 32].view(L, T, B, 32)[L - 1].permute(1, 0, 2).cpu()
+    assert torch.allclose(out_tc, ro, atol=3e-5, rtol=1e-4), float((out_tc - ro).abs().max())
+    assert torch.allclose(s_tc, s_ff, atol=3e-5, rtol=1e-4), float((s_tc - s_ff).abs().max())

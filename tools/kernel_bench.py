@@ -50,12 +50,13 @@ def main():
         opt.step_count = 1
         o = opt.desc()
         fwd = lambda: lib.b200rnn_lstm_fwd(C.byref(d), ar.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 1, sp)
+        fwd_tc = lambda: lib.b200rnn_lstm_fwd_tc(C.byref(d), ar.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 1, sp)
         bwd = lambda: lib.b200rnn_lstm_bwd(C.byref(d), ar.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), y.data_ptr(),
                                            1.0 / B, None, None, None, buf["scratch"].data_ptr(), sp)
         upd = lambda: lib.b200rnn_fused_update(buf["scratch"].data_ptr(), buf["n_cta"], ar.numel, ar.flat.data_ptr(),
                                                opt.exp_avg.data_ptr(), opt.exp_avg_sq.data_ptr(), C.byref(o), None, None, sp)
         step = lambda: eng.train_step(x, y)
-        out[B] = {"fwd_us": time_it(fwd, flush), "bwd_us": time_it(bwd, flush), "update_us": time_it(upd, flush),
+        out[B] = {"fwd_us": time_it(fwd, flush), "fwd_tc_us": time_it(fwd_tc, flush), "bwd_us": time_it(bwd, flush), "update_us": time_it(upd, flush),
                   "step_us": time_it(step, flush), "n_cta_bwd": buf["n_cta"]}
         print(B, json.dumps(out[B]), flush=True)
 
