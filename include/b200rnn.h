@@ -185,6 +185,25 @@ int b200rnn_cast_bf16(const float* in, void* out, int64_t n, void* stream);
 int b200rnn_transpose_cast_bf16(const float* in, void* out, int32_t rows, int32_t cols, int64_t ld_in,
                                 int64_t ld_out, void* stream);
 
+/* ---- Large-hidden LSTM / GRU path (H % 8 == 0; csrc/rnn/rnn_large.cu): input projection over all
+ * timesteps, per-step recurrent projection and all weight-gradient products run on the tcgen05 GEMM
+ * (bf16 operands, fp32 accumulate / state), gates + cell update fused in one pointwise kernel per
+ * step; the time loop is driven natively.  x_tm is TIME-major [T,B,I].  Buffers are the caller's:
+ * size them with the *_bytes queries.  stash: per layer  bf16 X | gates | (GRU) h-projection |
+ * (LSTM) c | h fp32 | h bf16;  the top layer's h ([T,B,H] fp32) is the module output. */
+int64_t b200rnn_rnn_large_stash_bytes(const b200rnn_model_desc* d);
+int64_t b200rnn_rnn_large_scratch_bytes(const b200rnn_model_desc* d);
+/* Byte offset of layer l's fp32 h sequence [T,B,H] (and, LSTM, c sequence) inside the stash. */
+int64_t b200rnn_rnn_large_h_offset(const b200rnn_model_desc* d, int32_t layer);
+int64_t b200rnn_rnn_large_c_offset(const b200rnn_model_desc* d, int32_t layer);
+int b200rnn_rnn_large_fwd(const b200rnn_model_desc* d, const float* params, const float* x_tm,
+                          void* stash, void* scratch, void* stream);
+/* d_out_tm [T,B,H] / d_hn, d_cn [L,B,H] nullable; grad_out: d->n_params floats in parameter layout;
+ * dx_tm [T,B,I] nullable. */
+int b200rnn_rnn_large_bwd(const b200rnn_model_desc* d, const float* params, const float* x_tm,
+                          const void* stash, void* scratch, const float* d_out_tm, const float* d_hn,
+                          const float* d_cn, float* grad_out, float* dx_tm, void* stream);
+
 /* ---- L2 flush helper for benchmarking (writes `bytes` of scratch). */
 int b200rnn_l2_flush(void* scratch, int64_t bytes, void* stream);
 

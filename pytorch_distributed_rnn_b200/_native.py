@@ -90,6 +90,12 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_head_fwd": (i32, [vp, i64, vp, vp, vp, i32, i32, i32, vp, vp, vp]),
         "b200rnn_fused_update": (i32, [vp, i32, i64, vp, vp, vp, P(OptimDesc), vp, vp, vp]),
         "b200rnn_l2_flush": (i32, [vp, i64, vp]),
+        "b200rnn_rnn_large_stash_bytes": (i64, [P(ModelDesc)]),
+        "b200rnn_rnn_large_scratch_bytes": (i64, [P(ModelDesc)]),
+        "b200rnn_rnn_large_h_offset": (i64, [P(ModelDesc), i32]),
+        "b200rnn_rnn_large_c_offset": (i64, [P(ModelDesc), i32]),
+        "b200rnn_rnn_large_fwd": (i32, [P(ModelDesc), vp, vp, vp, vp, vp]),
+        "b200rnn_rnn_large_bwd": (i32, [P(ModelDesc), vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
         "b200rnn_gemm_bf16": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
         "b200rnn_gemm_status": (i32, [P(i32)]),
         "b200rnn_cast_bf16": (i32, [vp, vp, i64, vp]),

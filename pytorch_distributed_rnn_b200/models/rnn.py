@@ -7,8 +7,10 @@
 ``torch.manual_seed`` gives bit-identical initial weights to stock torch), same
 call signature and return values.  What differs is what runs underneath:
 
-* CUDA tensors -> the hand-written sm_100a kernels in ``csrc/rnn`` (one persistent
-  launch for the whole sequence and all layers), through :mod:`..ops.rnn_function`;
+* CUDA tensors -> the hand-written sm_100a kernels in ``csrc/rnn``: the persistent fused family
+  (:mod:`..ops.rnn_function`; H = 32 LSTM, one launch for the whole sequence and all layers) or the
+  large-hidden path on the tcgen05 GEMM (:mod:`..ops.rnn_large`; LSTM and GRU, H % 8 == 0); only
+  shapes outside both (H not a multiple of 8, explicit initial state) use the torch composite;
 * CPU tensors  -> ATen's ``lstm``/``gru`` (the reference's own native path), used
   for the gloo plumbing configuration and as the numerical oracle in tests.
 """
@@ -124,6 +126,9 @@ class FusedRNNBase(nn.Module):
             from ..ops import rnn_function
             if hx is None and rnn_function.fused_supported(self, x):
                 return rnn_function.fused_rnn(self, x)
+            from ..ops import rnn_large
+            if hx is None and rnn_large.large_supported(self, x):
+                return rnn_large.large_rnn(self, x)
             return rnn_composite(self.cell, x, w, self.num_layers, self.hidden_size, hx, self.batch_first)
         return self._aten(x, w, hx)
 
