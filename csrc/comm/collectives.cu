@@ -279,6 +279,36 @@ __global__ void barrier_kernel(Ctx c, uint32_t seq) {
   }
 }
 
+// K10 — one-sided parameter server.  The server rank only HOSTS the shared parameter vector in its
+// symmetric heap; workers pull it with peer loads and apply their optimizer step to it with
+// red.global.add over NVLink (per-worker Adam state stays on the worker, as every worker of the
+// reference owns its own remote optimizer instance).  No barrier between workers: asynchronous,
+// Hogwild-style, like src/motion/param_server (worker.py:44-59) — minus its four RPC round trips.
+__global__ void __launch_bounds__(kThreads) ps_push_kernel(
+    Ctx c, int server, long long heap_off, const float* __restrict__ rows, int n_rows, long long n, long long row_stride,
+    float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq, OptScalars o, float* __restrict__ metrics) {
+  const long long i = (long long)blockIdx.x * kThreads + threadIdx.x;
+  if (i >= n + 2) return;
+  float g = 0.0f;
+  for (int r = 0; r < n_rows; ++r) g += rows[(long long)r * row_stride + i];
+  if (i >= n) { if (metrics != nullptr) metrics[i - n] = g; return; }
+  g *= o.grad_scale;
+  float p = 0.0f;                       // apply_update on p = 0 yields the DELTA of this step
+  float m = exp_avg ? exp_avg[i] : 0.0f;
+  float v = exp_avg_sq ? exp_avg_sq[i] : 0.0f;
+  OptScalars od = o;
+  od.wd = 0.0f;                         // weight decay would need the remote value; not supported here
+  apply_update(od, g, p, m, v);
+  if (exp_avg) exp_avg[i] = m;
+  if (exp_avg_sq) exp_avg_sq[i] = v;
+  float* sp = reinterpret_cast<float*>(c.base[server] + c.off_heap + heap_off) + i;
+  atomicAdd(sp, p);                     // RED.ADD.F32 to peer memory
+}
+__global__ void __launch_bounds__(kThreads) ps_pull_kernel(Ctx c, int server, long long heap_off, float* __restrict__ dst, long long n) {
+  const volatile float* sp = reinterpret_cast<const volatile float*>(c.base[server] + c.off_heap + heap_off);
+  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += (long long)gridDim.x * kThreads) dst[i] = sp[i];
+}
+
 int check_ctx(const b200rnn_comm_ctx* c, const char* who) {
   B200_REQUIRE(c != nullptr, B200RNN_EINVAL, "%s: null context", who);
   B200_REQUIRE(c->world >= 1 && c->world <= B200RNN_MAX_PEERS && c->rank >= 0 && c->rank < c->world, B200RNN_EINVAL,
@@ -418,5 +448,35 @@ extern "C" int b200rnn_comm_status(const b200rnn_comm_ctx* ctx, int32_t* status,
   B200_CHECK_CUDA(cudaMemcpyAsync(status, (char*)ctx->base[ctx->rank] + ctx->off_status, 4, cudaMemcpyDeviceToHost,
                                   (cudaStream_t)stream));
   B200_CHECK_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  return B200RNN_OK;
+}
+
+extern "C" int b200rnn_comm_ps_push(const b200rnn_comm_ctx* ctx, int32_t server, int64_t heap_off, const float* rows,
+                                    int32_t n_rows, int64_t n_params, float* exp_avg, float* exp_avg_sq,
+                                    const b200rnn_optim_desc* opt, float* metrics, void* stream) {
+  int rc = check_ctx(ctx, "comm_ps_push");
+  if (rc) return rc;
+  B200_REQUIRE(rows && opt && n_rows >= 1 && n_params > 0 && server >= 0 && server < ctx->world && heap_off >= 0 &&
+               heap_off + n_params * 4 <= ctx->heap_bytes, B200RNN_EINVAL, "comm_ps_push: bad argument");
+  B200_REQUIRE(opt->kind != 0 || (exp_avg && exp_avg_sq && opt->step >= 1), B200RNN_EINVAL,
+               "comm_ps_push: Adam needs exp_avg/exp_avg_sq and step >= 1");
+  const OptScalars o = make_opt_scalars(opt);
+  const int64_t blocks = (n_params + 2 + kThreads - 1) / kThreads;
+  ps_push_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(to_dev(ctx), server, heap_off, rows, n_rows, n_params,
+                                                                          n_params + 2, exp_avg, exp_avg_sq, o, metrics);
+  B200_CHECK_LAUNCH();
+  return B200RNN_OK;
+}
+
+extern "C" int b200rnn_comm_ps_pull(const b200rnn_comm_ctx* ctx, int32_t server, int64_t heap_off, float* dst,
+                                    int64_t n_params, void* stream) {
+  int rc = check_ctx(ctx, "comm_ps_pull");
+  if (rc) return rc;
+  B200_REQUIRE(dst && n_params > 0 && server >= 0 && server < ctx->world && heap_off >= 0 &&
+               heap_off + n_params * 4 <= ctx->heap_bytes, B200RNN_EINVAL, "comm_ps_pull: bad argument");
+  int64_t blocks = (n_params + kThreads - 1) / kThreads;
+  if (blocks > 4 * num_sms()) blocks = 4 * num_sms();
+  ps_pull_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(to_dev(ctx), server, heap_off, dst, n_params);
+  B200_CHECK_LAUNCH();
   return B200RNN_OK;
 }

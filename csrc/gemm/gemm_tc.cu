@@ -28,12 +28,15 @@ namespace {
 
 using namespace tc;
 
-constexpr int BM = 128, BN = 128, BK = 64, STAGES = 4;
-constexpr int TILE_BYTES = BM * BK * 2;           // 16 KiB per operand per stage
-constexpr int SMEM_BYTES = STAGES * 2 * TILE_BYTES + 256 + 1024;
+constexpr int BM = 128, BK = 64, STAGES = 4;
+constexpr int TILE_BYTES = BM * BK * 2;           // 16 KiB for the A tile per stage
+// BN = 128 for square-ish problems; BN = 32 for skinny ones (M <= 128: the per-timestep recurrent
+// projection h[B,H] x W_hh^T) so that N / 32 CTAs cover the SMs instead of N / 128.
+template <int BN> constexpr int smem_bytes() { return STAGES * (TILE_BYTES + BN * BK * 2) + 256 + 1024; }
 
 __device__ int g_gemm_error = 0;
 
+template <int BN>
 __global__ void __launch_bounds__(256, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  void* __restrict__ Cout, const float* __restrict__ bias, int M, int N, int K, int ldc,
@@ -41,8 +44,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
+  constexpr int B_TILE = BN * BK * 2;
+  constexpr int TM_COLS = BN < 32 ? 32 : BN;
   uint8_t* sB = smem + STAGES * TILE_BYTES;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + 2 * STAGES * TILE_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * (TILE_BYTES + B_TILE));
   uint64_t* empty = full + STAGES;
   uint64_t* tmem_full = empty + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
@@ -57,7 +62,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     mbar_init(tmem_full, 1);
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc<BN>(tmem_slot);
+  if (warp == 2) tmem_alloc<TM_COLS>(tmem_slot);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
@@ -69,9 +74,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       const int s = kb % STAGES;
       const uint32_t ph = (kb / STAGES) & 1;
       if (!mbar_wait(&empty[s], ph ^ 1)) { atomicExch(&g_gemm_error, 1); break; }
-      mbar_expect_tx(&full[s], 2 * TILE_BYTES);
+      mbar_expect_tx(&full[s], TILE_BYTES + B_TILE);
       tma_load_2d(sA + s * TILE_BYTES, &tma_a, &full[s], kb * BK, m0);
-      tma_load_2d(sB + s * TILE_BYTES, &tma_b, &full[s], kb * BK, n0);
+      tma_load_2d(sB + s * B_TILE, &tma_b, &full[s], kb * BK, n0);
     }
   } else if (warp == 1 && lane == 0) {
     // ===== MMA issuer =====
@@ -82,7 +87,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       const uint32_t ph = (kb / STAGES) & 1;
       if (!mbar_wait(&full[s], ph)) { atomicExch(&g_gemm_error, 2); ok = false; break; }
       tc_fence_after_sync();
-      const uint32_t a0 = smem_u32(sA + s * TILE_BYTES), b0 = smem_u32(sB + s * TILE_BYTES);
+      const uint32_t a0 = smem_u32(sA + s * TILE_BYTES), b0 = smem_u32(sB + s * B_TILE);
 #pragma unroll
       for (int k = 0; k < BK / 16; ++k) {
         // 128B-swizzled K-major tile: 8-row groups 1024 B apart; a K step of 16 bf16 = +32 B
@@ -127,7 +132,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   }
   tc_fence_before_sync();
   __syncthreads();
-  if (warp == 2) tmem_dealloc<BN>(tmem_base);
+  if (warp == 2) tmem_dealloc<TM_COLS>(tmem_base);
 }
 
 // fp32 -> bf16 cast, optionally transposing [R, C] -> [C, R] (operands of the dW GEMMs)
@@ -164,14 +169,14 @@ EncodeTiled get_encode() {
   return fn;
 }
 
-int make_map(CUtensorMap* map, const void* ptr, int rows, int k, int ld, const char* what) {
+int make_map(CUtensorMap* map, const void* ptr, int rows, int k, int ld, int box_rows, const char* what) {
   EncodeTiled enc = get_encode();
   B200_REQUIRE(enc != nullptr, B200RNN_ECUDA, "gemm: cuTensorMapEncodeTiled entry point not available");
   B200_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (ld % 8) == 0, B200RNN_EINVAL,
                "gemm: operand %s must be 16-byte aligned with a leading dimension multiple of 8 (ld=%d)", what, ld);
   const cuuint64_t dims[2] = {(cuuint64_t)k, (cuuint64_t)rows};
   const cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)BM};
+  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -189,18 +194,22 @@ extern "C" int b200rnn_gemm_bf16(const void* A, const void* B, void* C, const fl
                                  int32_t K, int32_t lda, int32_t ldb, int32_t ldc, int32_t accumulate,
                                  int32_t c_is_bf16, void* stream) {
   B200_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, B200RNN_EINVAL, "gemm_bf16: bad argument");
+  const bool skinny = (M <= BM) && ((N + 127) / 128 < num_sms() / 2) && N >= 32;
+  const int bn = skinny ? 32 : 128;
   CUtensorMap ma, mb;
-  int rc = make_map(&ma, A, M, K, lda, "A");
+  int rc = make_map(&ma, A, M, K, lda, BM, "A");
   if (rc) return rc;
-  rc = make_map(&mb, B, N, K, ldb, "B");
+  rc = make_map(&mb, B, N, K, ldb, bn, "B");
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<128>()));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<32>()));
     attr_set = true;
   }
-  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM);
-  gemm_bf16_kernel<<<grid, 256, SMEM_BYTES, (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16);
+  dim3 grid((N + bn - 1) / bn, (M + BM - 1) / BM);
+  if (skinny) gemm_bf16_kernel<32><<<grid, 256, smem_bytes<32>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16);
+  else gemm_bf16_kernel<128><<<grid, 256, smem_bytes<128>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16);
   B200_CHECK_LAUNCH();
   return B200RNN_OK;
 }

@@ -292,6 +292,16 @@ int b200rnn_comm_broadcast(const b200rnn_comm_ctx* ctx, uint32_t seq, int64_t he
 int b200rnn_comm_put(const b200rnn_comm_ctx* ctx, uint32_t seq, int32_t dst, const void* src,
                      int64_t heap_off, int64_t bytes, void* stream);
 int b200rnn_comm_wait(const b200rnn_comm_ctx* ctx, uint32_t seq, int32_t src, void* stream);
+/* K10: one-sided parameter server (src/motion/param_server/*).  The server rank hosts the shared
+ * parameters at heap offset heap_off of ITS symmetric heap and does nothing else.  ps_pull copies them
+ * into dst with peer loads; ps_push reduces the worker's gradient rows, runs the worker's OWN
+ * optimizer state (exp_avg / exp_avg_sq live on the worker) and adds the resulting parameter delta to
+ * the server's vector with red.global.add over NVLink.  Asynchronous: no ordering between workers. */
+int b200rnn_comm_ps_push(const b200rnn_comm_ctx* ctx, int32_t server, int64_t heap_off, const float* rows,
+                         int32_t n_rows, int64_t n_params, float* exp_avg, float* exp_avg_sq,
+                         const b200rnn_optim_desc* opt, float* metrics, void* stream);
+int b200rnn_comm_ps_pull(const b200rnn_comm_ctx* ctx, int32_t server, int64_t heap_off, float* dst,
+                         int64_t n_params, void* stream);
 /* Device-side barrier across all ranks. */
 int b200rnn_comm_barrier(const b200rnn_comm_ctx* ctx, uint32_t seq, void* stream);
 /* Reads this rank's watchdog status word (synchronises the stream): 0 = ok, else a bit mask of

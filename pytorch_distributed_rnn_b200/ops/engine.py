@@ -50,7 +50,7 @@ class FusedTrainEngine:
         self.comm = comm
         self.arena = arena if arena is not None else (optimizer.arena if optimizer is not None else ParamArena(model))
         self.optimizer = optimizer if optimizer is not None else FusedAdam(self.arena, lr=lr)
-        self.world = 1 if comm is None else comm.world
+        self.world = 1 if comm is None else getattr(comm, "grad_world", comm.world)
         self._bufs: Dict[Tuple[int, int], dict] = {}
         self.metrics = torch.zeros(self.METRIC_RING, 2, dtype=torch.float32, device=self.device)
         self.eval_metrics = torch.zeros(256, dtype=torch.float32, device=self.device)
@@ -110,7 +110,7 @@ class FusedTrainEngine:
         opt.step_count += 1
         slot = self.metrics[self.n_steps % self.METRIC_RING]
         o = opt.desc(grad_scale=1.0 / self.world)
-        if self.comm is None or self.world == 1:
+        if self.comm is None or (self.world == 1 and not getattr(self.comm, "always", False)):
             _native.check(self.lib.b200rnn_fused_update(
                 buf["scratch"].data_ptr(), buf["n_cta"], a.numel, a.flat.data_ptr(), opt.exp_avg.data_ptr(),
                 opt.exp_avg_sq.data_ptr(), C.byref(o), None, slot.data_ptr(), sp), "fused_update")

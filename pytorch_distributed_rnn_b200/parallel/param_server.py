@@ -13,9 +13,16 @@ checkpoint.  All of that is kept, except where the 
   returns the fresh parameters.  One request/response per step instead of the reference's
   four RPC round trips (forward, backward, gradient check, optimizer step; S13-S16).
 
-Transport: ``torch.distributed`` point-to-point over gloo (any-source receive on the server;
-host-pinned staging when the workers compute on GPUs) carrying one flat fp32 message per
-direction.  CLI: ``parameter-server --world-size W --rank R
+Transport, two forms:
+
+* GPUs (K10, the product path): ONE-SIDED over NVLink.  The server process only allocates the shared
+  parameter vector inside its symmetric heap and then idles; a worker's step is fused forward ->
+  fused backward -> ``b200rnn_comm_ps_push`` (reduce its gradient rows, run ITS Adam state, add the
+  resulting delta to the server's vector with ``red.global.add`` over NVLink) ->
+  ``b200rnn_comm_ps_pull`` (peer loads of the fresh parameters).  No server CPU or kernel is involved
+  in a step; the end of training is signalled with the K9 put primitive.
+* CPU (plumbing): ``torch.distributed`` point-to-point over gloo (any-source receive on the server)
+  carrying one flat fp32 message per direction.  CLI: ``parameter-server --world-size W --rank R
 [--master-address localhost] [--master-port 29500]`` — one invocation per node, like the
 reference (param_server/__init__.py:11-37).
 """
@@ -86,6 +93,49 @@ class ServerState:
         p.addcdiv_(st["m"], denom, value=-self.lr / bc1)
 
 
+def _symm_comm(rank: int, world_size: int, dev: torch.device):
+    from .process_group import RankInfo
+    from .symm import SymmComm
+    return SymmComm(RankInfo(rank, world_size, dev.index or 0, dev, "gloo"), inbox_floats=1 << 16, heap_bytes=64 << 20)
+
+
+class PSWorkerComm:
+    """Engine hook of a GPU worker: push (reduce + own Adam + remote add) then pull."""
+    kind = "ps"
+    grad_world = 1      # no averaging: every worker applies its own full step (asynchronous SGD)
+    always = True
+
+    def __init__(self, comm, heap_off: int, server: int = 0):
+        self.comm, self.heap_off, self.server = comm, heap_off, server
+        self.world, self.rank, self.device = comm.world, comm.rank, comm.device
+
+    def pull(self, arena) -> None:
+        self.comm.ps_pull(arena.flat[:arena.numel], self.server, self.heap_off)
+
+    def allreduce_update(self, rows, n_rows, arena, opt, optdesc, metrics_slot) -> None:
+        self.comm.ps_push(rows, n_rows, arena.numel, opt, optdesc, metrics_slot, self.server, self.heap_off)
+        self.pull(arena)
+
+
+def _run_parameter_server_gpu(rank, world_size, dev, input_dim, hidden_dim, layer_dim, output_dim, seed):
+    import time
+    comm = _symm_comm(rank, world_size, dev)
+    if seed is not None:
+        torch.manual_seed(seed)
+    model = MotionModel(input_dim, hidden_dim, layer_dim, output_dim).to(dev)
+    arena = comm.make_arena(model)           # the shared vector lives in the server's symmetric heap
+    torch.cuda.synchronize(dev)
+    dist.barrier()                           # workers may pull from now on
+    print("RPC initialized! Running parameter server... (one-sided NVLink mode: the server only hosts memory)")
+    while any(comm.signal_value(w) < 1 for w in range(1, world_size)):
+        time.sleep(0.005)
+    print("RPC shutdown on parameter server. (workers finished; parameter checksum %.6f)" % float(arena.flat[:arena.numel].double().sum()))
+    dist.barrier()
+    comm.close()
+    dist.destroy_process_group()
+    return arena
+
+
 def run_parameter_server(rank, world_size, input_dim, hidden_dim, layer_dim, output_dim, lr,
                          device: Optional[str] = None, seed: Optional[int] = None):
     dev = _pick_device(rank, device)
@@ -93,6 +143,8 @@ def run_parameter_server(rank, world_size, input_dim, hidden_dim, layer_dim, out
         torch.cuda.set_device(dev)
     print("PS master initializing RPC")
     _init_pg(rank, world_size, dev)
+    if dev.type == "cuda":
+        return _run_parameter_server_gpu(rank, world_size, dev, input_dim, hidden_dim, layer_dim, output_dim, seed)
     if seed is not None:
         torch.manual_seed(seed)
     model = MotionModel(input_dim, hidden_dim, layer_dim, output_dim).to(dev)
@@ -134,14 +186,30 @@ class ParameterWorkerTrainer(Trainer):
                          sampler=ShardedEpochSampler(len(training_set), num_replicas=world_size, rank=rank),
                          device=device)
         P = self.arena.numel
-        self._msg = torch.zeros(P + 1, dtype=torch.float32)   # host staging (pinned when a GPU is present)
+        if self._ps is not None:
+            dist.barrier()                    # the server's arena exists and is initialised
+            self._ps.pull(self.arena)
+            return
+        self._msg = torch.zeros(P + 1, dtype=torch.float32)
         self._reply = torch.zeros(P, dtype=torch.float32)
-        if self.device.type == "cuda":
-            self._msg, self._reply = self._msg.pin_memory(), self._reply.pin_memory()
         self._pull()
 
+    def _get_arena(self):
+        if self.device.type == "cuda":
+            self._symm = _symm_comm(self.rank, self.world_size, self.device)
+            arena = self._symm.make_arena(self._core_model())   # same heap offset as on the server
+            self._ps = PSWorkerComm(self._symm, arena.heap_off)
+            return arena
+        self._ps = None
+        return super()._get_arena()
+
+    def _get_comm(self):
+        return self._ps
+
     def _get_engine(self):
-        return None  # gradients must surface between backward and the (remote) optimizer step
+        if self._ps is not None:
+            return super()._get_engine()   # fused kernels; the optimizer step is the one-sided push
+        return None  # CPU: gradients must surface between backward and the (remote) optimizer step
 
     def _get_formatter(self, epochs):
         return TrainingMessageFormatter(epochs, self.rank)
@@ -171,6 +239,13 @@ class ParameterWorkerTrainer(Trainer):
         return torch.stack([loss.detach() * labels.numel(), correct.to(loss.dtype)])
 
     def finish(self):
+        if self._ps is not None:
+            torch.cuda.synchronize(self.device)
+            self._symm.put(torch.ones(1, device=self.device), dst=0)   # K9: "done" signal to the server
+            torch.cuda.synchronize(self.device)
+            dist.barrier()
+            self._symm.close()
+            return
         self._msg[0] = OP_DONE
         dist.send(self._msg, dst=0)
 

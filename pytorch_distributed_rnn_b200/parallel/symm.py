@@ -195,6 +195,25 @@ class SymmComm:
         t.view(-1).view(torch.uint8).copy_(self.heap[off:off + nbytes])
         return t
 
+    # ---- K10: one-sided parameter server primitives ----
+    def ps_pull(self, dst: torch.Tensor, server: int, heap_off: int) -> None:
+        _native.check(self.lib.b200rnn_comm_ps_pull(C.byref(self.ctx), server, heap_off, dst.data_ptr(), dst.numel(),
+                                                    self._sp()), "comm_ps_pull")
+        _native.count_launch()
+
+    def ps_push(self, rows: torch.Tensor, n_rows: int, n_params: int, opt, optdesc, metrics_slot, server: int,
+                heap_off: int) -> None:
+        _native.check(self.lib.b200rnn_comm_ps_push(C.byref(self.ctx), server, heap_off, rows.data_ptr(), n_rows, n_params,
+                                                    opt.exp_avg.data_ptr(), opt.exp_avg_sq.data_ptr(), C.byref(optdesc),
+                                                    _native.ptr(metrics_slot), self._sp()), "comm_ps_push")
+        _native.count_launch()
+
+    def signal_value(self, src: int) -> int:
+        """Host read of the K9 signal counter written by rank ``src`` (synchronises)."""
+        flags = torch.as_tensor(_External(self.local_base + self.ctx.off_flags_sig, 4 * _native.MAX_PEERS),
+                                device=self.device).view(torch.int32)
+        return int(flags[src].item())
+
     def check(self) -> None:
         """Raise if a watchdog fired (a peer's flag never arrived)."""
         st = C.c_int32(0)

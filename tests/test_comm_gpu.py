@@ -123,3 +123,37 @@ def test_native_bootstrap_two_processes():
     ps = [subprocess.Popen([sys.executable, "-c", code, str(r)], stdout=subprocess.PIPE, text=True) for r in range(2)]
     outs = [p.communicate(timeout=90)[0].strip() for p in ps]
     assert outs == ["rank0|rank1", "rank0|rank1"]
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_gpu_parameter_server_one_sided(tmp_path):
+    """K10: server + 2 workers as separate processes (the reference's launch style), NVLink one-sided."""
+    import os
+    import re
+    import subprocess
+    from pytorch_distributed_rnn_b200.data import synthetic
+    from pytorch_distributed_rnn_b200.parallel.launch import free_port
+    synthetic.write_dataset(tmp_path / "ds", train=384, valid=20, test=30)
+    port = free_port()
+    procs = []
+    for rank in range(3):
+        cmd = [sys.executable, "-m", "pytorch_distributed_rnn_b200", "--dataset-path", str(tmp_path / "ds"), "--epochs", "2",
+               "--batch-size", "64", "--seed", "1", "--no-validation", "--learning-rate", "0.01",
+               "parameter-server", "--world-size", "3", "--rank", str(rank), "--master-address", "127.0.0.1",
+               "--master-port", str(port)]
+        procs.append(subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                                      env={**os.environ, "PYTHONPATH": str(ROOT)}))
+    outs = []
+    try:
+        outs = [p.communicate(timeout=300) for p in procs]
+    finally:
+        for p in procs:
+            if p.poll() is None:
+                p.kill()
+    for p, (o, e) in zip(procs, outs):
+        assert p.returncode == 0, o[-2000:] + e[-3000:]
+    assert "one-sided NVLink mode" in outs[0][0] and "RPC shutdown on parameter server" in outs[0][0]
+    for r in (1, 2):
+        losses = [float(m) for m in re.findall(r"Loss: ([\d.]+)", outs[r][1])]
+        assert len(losses) == 4 and losses[-1] < losses[0], losses   # 2 epochs x 128/64 batches, learning
