@@ -163,7 +163,9 @@ class SymmComm:
         if off is None or off % 16 != 0:
             # symmetric offsets must match on every rank: all ranks take the same branch for the same call
             staged, off = self.heap, (self._stage_off if nbytes <= self._stage_bytes else self.heap_alloc(nbytes))
-            self.heap[off:off + nbytes].copy_(t.contiguous().view(-1).view(torch.uint8))
+            if self.rank == root:   # only the root fills its staging slot: a peer writing its own slot could
+                #                     overwrite data the root has already delivered there
+                self.heap[off:off + nbytes].copy_(t.contiguous().view(-1).view(torch.uint8))
         self._seq_bc += 1
         _native.check(self.lib.b200rnn_comm_broadcast(C.byref(self.ctx), self._seq_bc, off, nbytes, root, self._sp()),
                       "comm_broadcast")
