@@ -16,8 +16,8 @@ Rank 0 prints ONE JSON line.  Two measurements per run:
   The step is K11 gather from the device-resident dataset -> fused forward -> fused
   head/CE/backward -> fused grad-reduce/all-reduce/Adam: 4 launches of this repo's kernels.
 * ``e2e``     — wall clock through the public API a user calls
-  (``FusedTrainEngine.train_step_host``): every step copies that step's inputs from pinned
-  host memory to the GPU and reads the step's loss back to the host.
+  (``FusedTrainEngine.train_steps_host``): every step copies that step's inputs from pinned
+  host memory to the GPU and reads the step's loss back to the host (copies pipelined with compute).
 
 ``--impl reference`` runs the UNMODIFIED reference (installed at baseline/_ref) through its own
 Trainer loop on the same GPUs (stock torch cuDNN LSTM + NCCL DistributedDataParallel); see
@@ -197,13 +197,15 @@ def run_own(args):
     for s in range(ring):
         i = step_indices(s)
         host.append((x_all[i].contiguous().pin_memory(), y_all[i].contiguous().view(-1).pin_memory()))
-    for s in range(max(W, 3)):
-        engine.train_step_host(*host[s % ring])
+    for _ in engine.train_steps_host(host[s % ring] for s in range(max(W, 3))):
+        pass
     barrier_sync(world, dev)
     t_c = time.time()
     t0 = time.perf_counter()
-    for s in range(K):
-        loss, correct = engine.train_step_host(*host[s % ring])
+    n_results = 0
+    for loss, correct in engine.train_steps_host(host[s % ring] for s in range(K)):
+        n_results += 1
+    assert n_results == K
     barrier_sync(world, dev)
     e2e_s = time.perf_counter() - t0
     t_d = time.time()
@@ -231,8 +233,9 @@ def run_own(args):
                        "baseline_number": "1922.7 samples/s = 6912/3.595 s, reference local bs1440 on its fast host"},
             "e2e": {"value": GLOBAL_BATCH * K / e2e_s, "unit": "samples/s", "ms_per_step": 1e3 * e2e_s / K,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "api": "FusedTrainEngine.train_step_host(x_pinned, y_pinned) -> (loss, correct)",
-                    "inputs": f"{ring} pre-collated pinned host batches, one H2D copy + one D2H loss read per step"},
+                    "api": "FusedTrainEngine.train_steps_host(host_batches) -> yields (loss, correct) per step",
+                    "inputs": f"{ring} pre-collated pinned host batches; every step: H2D copy of its batch (side stream, "
+                              "overlapping the previous step) + D2H read of its loss (one-step lag)"},
             "gpu_launches": launches,
             "launches_per_step": launches / K,
             "clocks": clocks,

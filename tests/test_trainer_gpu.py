@@ -48,3 +48,17 @@ def test_deferred_logging_same_lines(caplog, tmp_path):
     _, _, _, s1, _ = _run("cuda", caplog, tmp_path)
     _, _, _, s2, _ = _run("cuda", caplog, tmp_path, deferred=True)
     assert s1 == s2
+
+
+def test_pipelined_host_steps_match_serial_steps():
+    from pytorch_distributed_rnn_b200.ops.engine import FusedTrainEngine
+    xs = [torch.randn(96, 32, 9).pin_memory() for _ in range(5)]
+    ys = [torch.randint(0, 6, (96,)).pin_memory() for _ in range(5)]
+    torch.manual_seed(3)
+    a = FusedTrainEngine(MotionModel(9, 32, 2, 6).cuda())
+    torch.manual_seed(3)
+    b = FusedTrainEngine(MotionModel(9, 32, 2, 6).cuda())
+    serial = [a.train_step_host(x, y) for x, y in zip(xs, ys)]
+    piped = list(b.train_steps_host(zip(xs, ys)))
+    assert serial == piped
+    assert torch.equal(a.arena.flat, b.arena.flat)
