@@ -11,8 +11,8 @@ a per-message latency (one-shot: x1, two-shot: x2 — cf. DDP's ~25 serialized l
 Horovod's extra negotiation rounds).
 
 Launch (N ranks):  torchrun --nproc-per-node N bench/allreduce_sweep.py [--out results.json]
-Timing: CUDA events on the launching stream, per size 20 iterations after 5 warm-ups, max over
-ranks.  Roofline per size: bytes that must cross NVLink per rank / 770 GB/s (measured peer copy
+Timing: CUDA events on the launching stream around 8 back-to-back calls, per size 20 such
+measurements after 5 warm-ups, median, max over ranks.  Roofline per size: bytes that must cross NVLink per rank / 770 GB/s (measured peer copy
 bandwidth, B200_PROFILING.md); one-shot sends (W-1)*S, two-shot 2*(W-1)/W*S.
 """
 from __future__ import annotations
@@ -33,6 +33,9 @@ from pytorch_distributed_rnn_b200.parallel.symm import SymmComm  # noqa: E402
 NVLINK_GBS = 770.0
 
 
+REPS = 8   # calls per event pair: the GPU queue stays full, so host launch cost (~20 us of Python) is not timed
+
+
 def timed(fn, iters, warm, dev):
     for _ in range(warm):
         fn()
@@ -41,9 +44,12 @@ def timed(fn, iters, warm, dev):
     ts = []
     for _ in range(iters):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(); fn(); b.record()
+        a.record()
+        for _ in range(REPS):
+            fn()
+        b.record()
         torch.cuda.synchronize(dev)
-        ts.append(a.elapsed_time(b) * 1e3)
+        ts.append(a.elapsed_time(b) * 1e3 / REPS)
     t = torch.tensor([sorted(ts)[len(ts) // 2]], device=dev, dtype=torch.float64)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t)
@@ -80,7 +86,7 @@ def main():
             slot = torch.zeros(2, device=dev)
             row = {"bytes": nbytes, "world": world, "delay_us": delay}
             for algo, name in ((1, "oneshot"), (2, "twoshot")):
-                if algo == 1 and (n + 255) // 256 > comm.ctx.max_blocks:
+                if algo == 1 and (n + 1023) // 1024 > comm.ctx.max_blocks:
                     continue
                 comm.algo = algo
 

@@ -81,30 +81,68 @@ __device__ __forceinline__ void wait_flag(const Ctx& c, const uint32_t* f, uint3
 }
 
 // ---------------------------------------------------------------------------
+// Element access helpers: 4 consecutive elements per thread, 128-bit where alignment allows.
+// ---------------------------------------------------------------------------
+struct F4 { float v[4]; };
+__device__ __forceinline__ F4 reduce_rows4(const float* __restrict__ rows, int n_rows, long long row_stride, long long i, long long n_valid) {
+  F4 r; r.v[0] = r.v[1] = r.v[2] = r.v[3] = 0.0f;
+  if (n_rows == 1 && ((reinterpret_cast<uintptr_t>(rows + i) & 15) == 0) && i + 3 < n_valid) {
+    const float4 t = *reinterpret_cast<const float4*>(rows + i);
+    r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w;
+    return r;
+  }
+  for (int k = 0; k < n_rows; ++k) {
+    const float* p = rows + (long long)k * row_stride + i;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) if (i + e < n_valid) r.v[e] += p[e];
+  }
+  return r;
+}
+__device__ __forceinline__ void store4(float* dst, const F4& x, long long i, long long n_valid) {
+  if (i + 3 < n_valid && (reinterpret_cast<uintptr_t>(dst + i) & 15) == 0) {
+    *reinterpret_cast<float4*>(dst + i) = make_float4(x.v[0], x.v[1], x.v[2], x.v[3]);
+  } else {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) if (i + e < n_valid) dst[i + e] = x.v[e];
+  }
+}
+__device__ __forceinline__ F4 load4_cg(const float* src, long long i, long long n_valid) {
+  F4 r;
+  if (i + 3 < n_valid && (reinterpret_cast<uintptr_t>(src + i) & 15) == 0) {
+    const float4 t = __ldcg(reinterpret_cast<const float4*>(src + i));
+    r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w;
+  } else {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) r.v[e] = (i + e < n_valid) ? __ldcg(src + i + e) : 0.0f;
+  }
+  return r;
+}
+
+// ---------------------------------------------------------------------------
 // One-shot: every rank pushes its whole (locally reduced) vector into every peer's inbox,
 // then sums the W inbox slices it received.  1 NVLink one-way latency; traffic W*n per rank:
 // the right trade for the 56.6 KB gradient of the reference's model.
-// Block b handles elements [b*256, (b+1)*256); flags are per (source, block), so blocks are
-// independent and no grid-wide synchronisation exists.
+// Block b handles elements [b*1024, (b+1)*1024) (4 per thread, 128-bit peer stores); flags are per
+// (source, block), so blocks are independent and no grid-wide synchronisation exists.
 // ---------------------------------------------------------------------------
 template <bool UPDATE>
 __global__ void __launch_bounds__(kThreads) oneshot_kernel(
     Ctx c, uint32_t seq, const float* __restrict__ rows, int n_rows, long long n, long long row_stride,
     float* buf /* UPDATE: params, else in/out vector */, float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
     OptScalars o, float scale, float* __restrict__ metrics) {
-  const long long i = (long long)blockIdx.x * kThreads + threadIdx.x;
-  const bool live = i < n;
-  float g = 0.0f;
+  const long long i = ((long long)blockIdx.x * kThreads + threadIdx.x) * kElems;
+  F4 g;
   if (UPDATE) {
-    if (i < n + 2) {
-      for (int r = 0; r < n_rows; ++r) g += rows[(long long)r * row_stride + i];
-      if (i >= n && metrics != nullptr) metrics[i - n] = g;  // loss sum / correct count stay local
+    g = reduce_rows4(rows, n_rows, row_stride, i, n + 2);
+    if (metrics != nullptr) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) if (i + e >= n && i + e < n + 2) metrics[i + e - n] = g.v[e];   // stay local
     }
-  } else if (live) {
-    g = buf[i];
+  } else {
+    g = reduce_rows4(buf, 1, 0, i, n);
   }
-  if (live) {
-    for (int p = 0; p < c.world; ++p) inbox(c, p, seq, c.rank)[i] = g;   // peer stores (incl. self)
+  if (i < n) {
+    for (int p = 0; p < c.world; ++p) store4(inbox(c, p, seq, c.rank), g, i, n);   // peer stores (incl. self)
   }
   __threadfence_system();
   __syncthreads();
@@ -114,101 +152,124 @@ __global__ void __launch_bounds__(kThreads) oneshot_kernel(
   }
   if (threadIdx.x < c.world) wait_flag(c, flags_ar(c, c.rank, threadIdx.x, blockIdx.x), seq, threadIdx.x);
   __syncthreads();
-  if (!live) return;
-  float sum = 0.0f;
-  for (int s = 0; s < c.world; ++s) sum += __ldcg(inbox(c, c.rank, seq, s) + i);   // fixed rank order
-  if (UPDATE) {
-    const float gg = sum * o.grad_scale;
-    float p = buf[i];
-    float m = exp_avg ? exp_avg[i] : 0.0f;
-    float v = exp_avg_sq ? exp_avg_sq[i] : 0.0f;
-    apply_update(o, gg, p, m, v);
-    buf[i] = p;
-    if (exp_avg) exp_avg[i] = m;
-    if (exp_avg_sq) exp_avg_sq[i] = v;
-  } else {
-    buf[i] = sum * scale;
+  if (i >= n) return;
+  F4 sum; sum.v[0] = sum.v[1] = sum.v[2] = sum.v[3] = 0.0f;
+  for (int s = 0; s < c.world; ++s) {   // fixed rank order => identical bits on every rank
+    const F4 t = load4_cg(inbox(c, c.rank, seq, s), i, n);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) sum.v[e] += t.v[e];
+  }
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const long long j = i + e;
+    if (j >= n) break;
+    if (UPDATE) {
+      float p = buf[j];
+      float m = exp_avg ? exp_avg[j] : 0.0f;
+      float v = exp_avg_sq ? exp_avg_sq[j] : 0.0f;
+      apply_update(o, sum.v[e] * o.grad_scale, p, m, v);
+      buf[j] = p;
+      if (exp_avg) exp_avg[j] = m;
+      if (exp_avg_sq) exp_avg_sq[j] = v;
+    } else {
+      buf[j] = sum.v[e] * scale;
+    }
   }
 }
 
+// Grid-wide barrier on a monotonically increasing local counter (all CTAs co-resident: grid = #SMs).
+__device__ __forceinline__ void grid_sync(const Ctx& c, unsigned int* counter, unsigned int target) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    atomicAdd(counter, 1u);
+    const long long t0 = clock64();
+    while ((int)(*reinterpret_cast<volatile unsigned int*>(counter) - target) < 0) {
+      if (clock64() - t0 > c.timeout) {   // CTAs not co-resident / lost: report instead of hanging
+        atomicOr(reinterpret_cast<unsigned int*>(c.base[c.rank] + c.off_status), 1u << 30);
+        break;
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
 // ---------------------------------------------------------------------------
-// Two-shot: reduce-scatter the gradient to its owning rank, run the optimizer on the owner's
-// shard, all-gather the UPDATED PARAMETERS by peer stores into every rank's (symmetric) arena.
-// Traffic 2(W-1)/W * n per rank.  Persistent grid: block k (1024 elements) is handled by CTA
-// k mod gridDim on every rank, in increasing k, which makes the cross-rank waits deadlock-free
-// as long as the grid is co-resident (grid <= #SMs).
+// Two-shot, bulk form: reduce-scatter the gradient to its owning rank (shard p -> rank p), run the
+// optimizer on the owner's shard, all-gather the UPDATED PARAMETERS by peer stores into every rank's
+// (symmetric) arena.  Traffic 2(W-1)/W * n per rank.  The whole grid (one CTA per SM) streams each
+// phase with 128-bit accesses; phases are separated by a local grid barrier and ONE flag per
+// (source, destination) pair — 2W flags per call instead of one per 1 KiB block.
 // ---------------------------------------------------------------------------
 template <bool UPDATE>
 __global__ void __launch_bounds__(kThreads) twoshot_kernel(
-    Ctx c, uint32_t seq, const float* __restrict__ rows, int n_rows, long long n, long long row_stride,
-    float* buf, long long buf_heap_off, float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
-    OptScalars o, float scale, float* __restrict__ metrics, int n_blocks, int blocks_per_rank) {
+    Ctx c, uint32_t seq, unsigned int sync_target, const float* __restrict__ rows, int n_rows, long long n,
+    long long row_stride, float* buf, long long buf_heap_off, float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
+    OptScalars o, float scale, float* __restrict__ metrics, long long shard) {
+  unsigned int* counter = reinterpret_cast<unsigned int*>(c.base[c.rank] + c.off_flags_bar) + 2 * B200RNN_MAX_PEERS + 1;
+  const long long tstride = (long long)gridDim.x * kThreads * kElems;
+  const long long t0 = ((long long)blockIdx.x * kThreads + threadIdx.x) * kElems;
   if (UPDATE && blockIdx.x == 0 && threadIdx.x < 2 && metrics != nullptr) {
     float g = 0.0f;
     for (int r = 0; r < n_rows; ++r) g += rows[(long long)r * row_stride + n + threadIdx.x];
     metrics[threadIdx.x] = g;
   }
-  for (int k = blockIdx.x; k < n_blocks; k += gridDim.x) {
-    const int owner = k / blocks_per_rank;
-    const long long base = (long long)k * kBlockElems + threadIdx.x * kElems;
-    const long long ibase = (long long)(k - owner * blocks_per_rank) * kBlockElems + threadIdx.x * kElems;
-    float g[kElems];
-#pragma unroll
-    for (int e = 0; e < kElems; ++e) {
-      const long long i = base + e;
-      float acc = 0.0f;
-      if (i < n) {
-        if (UPDATE) { for (int r = 0; r < n_rows; ++r) acc += rows[(long long)r * row_stride + i]; }
-        else acc = buf[i];
-      }
-      g[e] = acc;
+  // ---- phase 1: push shard p of my (row-reduced) vector into owner p's inbox ----
+  for (int dp = 1; dp <= c.world; ++dp) {
+    const int p = (c.rank + dp) % c.world;          // rotate so the W ranks hit W different owners
+    const long long lo = (long long)p * shard;
+    const long long hi = lo + shard < n ? lo + shard : n;
+    float* dst = inbox(c, p, seq, c.rank);
+    for (long long i = lo + t0; i < hi; i += tstride) {
+      const F4 g = UPDATE ? reduce_rows4(rows, n_rows, row_stride, i, hi) : reduce_rows4(buf, 1, 0, i, hi);
+      store4(dst - lo, g, i, hi);
     }
-    float* dst = inbox(c, owner, seq, c.rank) + ibase;
+  }
+  grid_sync(c, counter, sync_target - gridDim.x);
+  if (threadIdx.x == 0 && blockIdx.x < c.world) {
+    delay(c);
+    st_release_sys(flags_ar(c, blockIdx.x, c.rank, 0), seq);
+  }
+  // ---- phase 2: owner reduces its shard, applies the optimizer, broadcasts the new parameters ----
+  if (threadIdx.x < c.world) wait_flag(c, flags_ar(c, c.rank, threadIdx.x, 0), seq, threadIdx.x);
+  __syncthreads();
+  {
+    const long long lo = (long long)c.rank * shard;
+    const long long hi = lo + shard < n ? lo + shard : n;
+    for (long long i = lo + t0; i < hi; i += tstride) {
+      F4 sum; sum.v[0] = sum.v[1] = sum.v[2] = sum.v[3] = 0.0f;
+      for (int s = 0; s < c.world; ++s) {
+        const F4 t = load4_cg(inbox(c, c.rank, seq, s) - lo, i, hi);
 #pragma unroll
-    for (int e = 0; e < kElems; ++e) if (base + e < n) dst[e] = g[e];
-    __threadfence_system();
-    __syncthreads();
-    if (threadIdx.x == 0) { delay(c); st_release_sys(flags_ar(c, owner, c.rank, k), seq); }
-    if (owner == c.rank) {
-      if (threadIdx.x < c.world) wait_flag(c, flags_ar(c, c.rank, threadIdx.x, k), seq, threadIdx.x);
-      __syncthreads();
-      float out[kElems];
+        for (int e = 0; e < 4; ++e) sum.v[e] += t.v[e];
+      }
+      F4 out;
 #pragma unroll
-      for (int e = 0; e < kElems; ++e) {
-        const long long i = base + e;
-        float sum = 0.0f;
-        if (i < n) {
-          for (int s = 0; s < c.world; ++s) sum += __ldcg(inbox(c, c.rank, seq, s) + ibase + e);
-          if (UPDATE) {
-            float p = buf[i];
-            float m = exp_avg ? exp_avg[i] : 0.0f;
-            float v = exp_avg_sq ? exp_avg_sq[i] : 0.0f;
-            apply_update(o, sum * o.grad_scale, p, m, v);
-            if (exp_avg) exp_avg[i] = m;
-            if (exp_avg_sq) exp_avg_sq[i] = v;
-            sum = p;
-          } else {
-            sum *= scale;
-          }
+      for (int e = 0; e < 4; ++e) {
+        const long long j = i + e;
+        float r = sum.v[e] * scale;
+        if (UPDATE && j < hi) {
+          float p = buf[j];
+          float m = exp_avg ? exp_avg[j] : 0.0f;
+          float v = exp_avg_sq ? exp_avg_sq[j] : 0.0f;
+          apply_update(o, sum.v[e] * o.grad_scale, p, m, v);
+          if (exp_avg) exp_avg[j] = m;
+          if (exp_avg_sq) exp_avg_sq[j] = v;
+          r = p;
         }
-        out[e] = sum;
+        out.v[e] = r;
       }
-      for (int p = 0; p < c.world; ++p) {   // all-gather by peer stores (self included)
-        float* pd = reinterpret_cast<float*>(c.base[p] + c.off_heap + buf_heap_off);
-#pragma unroll
-        for (int e = 0; e < kElems; ++e) if (base + e < n) pd[base + e] = out[e];
+      for (int dp = 0; dp < c.world; ++dp) {   // all-gather by peer stores (self first)
+        const int p = (c.rank + dp) % c.world;
+        store4(reinterpret_cast<float*>(c.base[p] + c.off_heap + buf_heap_off), out, i, hi);
       }
-      __threadfence_system();
-      __syncthreads();
-      if (threadIdx.x == 0)
-        for (int p = 0; p < c.world; ++p) st_release_sys(flags_pr(c, p, k), seq);
     }
   }
-  // do not retire before every block of the vector has arrived from its owner
-  for (int k = blockIdx.x; k < n_blocks; k += gridDim.x) {
-    const int owner = k / blocks_per_rank;
-    if (owner != c.rank && threadIdx.x == 0) wait_flag(c, flags_pr(c, c.rank, k), seq, owner);
-  }
+  grid_sync(c, counter, sync_target);
+  if (threadIdx.x == 0 && blockIdx.x < c.world) st_release_sys(flags_pr(c, blockIdx.x, c.rank), seq);
+  // ---- phase 3: do not retire before every owner's shard has landed here ----
+  if (blockIdx.x == 0 && threadIdx.x < c.world) wait_flag(c, flags_pr(c, c.rank, threadIdx.x), seq, threadIdx.x);
 }
 
 // K8 broadcast on the symmetric heap: root copies its bytes into every peer's heap, then flags.
@@ -309,6 +370,18 @@ __global__ void __launch_bounds__(kThreads) ps_pull_kernel(Ctx c, int server, lo
   for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += (long long)gridDim.x * kThreads) dst[i] = sp[i];
 }
 
+// Host-side count of two-shot launches per symmetric region (its grid-barrier counter lives in the
+// region and only ever increases).  b200rnn_comm_layout-time callers reset it via b200rnn_comm_forget.
+struct SyncEntry { const void* base; unsigned int calls; };
+SyncEntry g_sync[64];
+int g_sync_n = 0;
+unsigned int next_sync_call(const void* base) {
+  for (int i = 0; i < g_sync_n; ++i) if (g_sync[i].base == base) return ++g_sync[i].calls;
+  if (g_sync_n < 64) { g_sync[g_sync_n].base = base; g_sync[g_sync_n].calls = 1; ++g_sync_n; return 1; }
+  g_sync[0].base = base; g_sync[0].calls = 1;
+  return 1;
+}
+
 int check_ctx(const b200rnn_comm_ctx* c, const char* who) {
   B200_REQUIRE(c != nullptr, B200RNN_EINVAL, "%s: null context", who);
   B200_REQUIRE(c->world >= 1 && c->world <= B200RNN_MAX_PEERS && c->rank >= 0 && c->rank < c->world, B200RNN_EINVAL,
@@ -344,11 +417,12 @@ static int launch_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, const flo
   OptScalars o{};
   if (update) o = make_opt_scalars(opt);
   const int64_t row_stride = n + 2;
-  const int64_t one_blocks = ((update ? n + 2 : n) + kThreads - 1) / kThreads;
+  const int64_t one_blocks = ((update ? n + 2 : n) + kBlockElems - 1) / kBlockElems;
   if (algo == B200RNN_ALGO_AUTO) {
     // one-shot moves W*n floats per rank but pays a single NVLink latency; two-shot moves
-    // 2(W-1)/W*n but pays two.  Crossover measured by bench/allreduce_sweep.py (profiles/).
-    algo = (n * 4 <= 256 * 1024 || ctx->world == 1) ? B200RNN_ALGO_ONESHOT : B200RNN_ALGO_TWOSHOT;
+    // 2(W-1)/W*n but pays two latencies and two grid barriers.  Crossover from the measured sweep
+    // (bench/allreduce_sweep.py, profiles/).
+    algo = (n * 4 <= 512 * 1024 || ctx->world == 1 || heap_off < 0) ? B200RNN_ALGO_ONESHOT : B200RNN_ALGO_TWOSHOT;
   }
   if (algo == B200RNN_ALGO_ONESHOT) {
     B200_REQUIRE(one_blocks <= ctx->max_blocks, B200RNN_ETOOBIG, "comm one-shot: %lld blocks exceed max_blocks=%d",
@@ -358,18 +432,19 @@ static int launch_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, const flo
     if (update) oneshot_kernel<true><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
     else oneshot_kernel<false><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
   } else {
-    const int64_t n_blocks = (n + kBlockElems - 1) / kBlockElems;
-    const int64_t bpr = (n_blocks + ctx->world - 1) / ctx->world;
-    B200_REQUIRE(n_blocks <= ctx->max_blocks, B200RNN_ETOOBIG, "comm two-shot: %lld blocks exceed max_blocks=%d",
-                 (long long)n_blocks, ctx->max_blocks);
-    B200_REQUIRE(bpr * kBlockElems <= ctx->inbox_floats, B200RNN_ETOOBIG,
-                 "comm two-shot: shard of %lld floats exceeds inbox capacity %lld", (long long)(bpr * kBlockElems),
+    int64_t shard = (n + ctx->world - 1) / ctx->world;
+    shard = (shard + 3) & ~int64_t(3);                       // 16-byte aligned shard starts
+    B200_REQUIRE(shard <= ctx->inbox_floats, B200RNN_ETOOBIG,
+                 "comm two-shot: shard of %lld floats exceeds inbox capacity %lld", (long long)shard,
                  (long long)ctx->inbox_floats);
-    B200_REQUIRE(heap_off >= 0 && heap_off + n * 4 <= ctx->heap_bytes, B200RNN_EINVAL,
-                 "comm two-shot: the vector must live in the symmetric heap (heap_off=%lld)", (long long)heap_off);
-    int grid = (int)(n_blocks < num_sms() ? n_blocks : num_sms());
-    if (update) twoshot_kernel<true><<<grid, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, heap_off, m, v, o, scale, metrics, (int)n_blocks, (int)bpr);
-    else twoshot_kernel<false><<<grid, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, heap_off, m, v, o, scale, metrics, (int)n_blocks, (int)bpr);
+    B200_REQUIRE(heap_off >= 0 && heap_off + n * 4 <= ctx->heap_bytes && (heap_off & 15) == 0, B200RNN_EINVAL,
+                 "comm two-shot: the vector must live in the symmetric heap, 16-byte aligned (heap_off=%lld)", (long long)heap_off);
+    // local grid barrier bookkeeping: fixed grid (one CTA per SM), monotonically increasing target
+    const int grid = num_sms();
+    B200_REQUIRE(ctx->world <= grid, B200RNN_EINVAL, "comm two-shot: world larger than the grid");
+    const unsigned int target = next_sync_call(ctx->base[ctx->rank]) * 2u * (unsigned)grid;
+    if (update) twoshot_kernel<true><<<grid, kThreads, 0, s>>>(c, seq, target, rows, n_rows, n, row_stride, buf, heap_off, m, v, o, scale, metrics, shard);
+    else twoshot_kernel<false><<<grid, kThreads, 0, s>>>(c, seq, target, rows, n_rows, n, row_stride, buf, heap_off, m, v, o, scale, metrics, shard);
   }
   B200_CHECK_LAUNCH();
   return B200RNN_OK;
@@ -478,5 +553,11 @@ extern "C" int b200rnn_comm_ps_pull(const b200rnn_comm_ctx* ctx, int32_t server,
   if (blocks > 4 * num_sms()) blocks = 4 * num_sms();
   ps_pull_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(to_dev(ctx), server, heap_off, dst, n_params);
   B200_CHECK_LAUNCH();
+  return B200RNN_OK;
+}
+
+extern "C" int b200rnn_comm_forget(const void* region_base) {
+  for (int i = 0; i < g_sync_n; ++i)
+    if (g_sync[i].base == region_base) { g_sync[i] = g_sync[g_sync_n - 1]; --g_sync_n; break; }
   return B200RNN_OK;
 }

@@ -302,6 +302,9 @@ int b200rnn_comm_ps_push(const b200rnn_comm_ctx* ctx, int32_t server, int64_t he
                          const b200rnn_optim_desc* opt, float* metrics, void* stream);
 int b200rnn_comm_ps_pull(const b200rnn_comm_ctx* ctx, int32_t server, int64_t heap_off, float* dst,
                          int64_t n_params, void* stream);
+/* Tell the library that a (new) symmetric region starts at region_base: resets its host-side
+ * bookkeeping for that address.  Call once after b200rnn_symm_create. */
+int b200rnn_comm_forget(const void* region_base);
 /* Device-side barrier across all ranks. */
 int b200rnn_comm_barrier(const b200rnn_comm_ctx* ctx, uint32_t seq, void* stream);
 /* Reads this rank's watchdog status word (synchronises the stream): 0 = ok, else a bit mask of

@@ -120,6 +120,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_comm_wait": (i32, [P(CommCtx), C.c_uint32, i32, vp]),
         "b200rnn_comm_ps_push": (i32, [P(CommCtx), i32, i64, vp, i32, i64, vp, vp, P(OptimDesc), vp, vp]),
         "b200rnn_comm_ps_pull": (i32, [P(CommCtx), i32, i64, vp, i64, vp]),
+        "b200rnn_comm_forget": (i32, [vp]),
         "b200rnn_comm_barrier": (i32, [P(CommCtx), C.c_uint32, vp]),
         "b200rnn_comm_status": (i32, [P(CommCtx), P(i32), vp]),
     }

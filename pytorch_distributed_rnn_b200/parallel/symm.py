@@ -91,6 +91,7 @@ class SymmComm:
         self.ctx = ctx
         self.region_bytes = region
         self.local_base = ptrs[self.rank]
+        self.lib.b200rnn_comm_forget(self.local_base)
         self.heap = torch.as_tensor(_External(self.local_base + ctx.off_heap, heap_bytes), device=self.device)
         self._heap_top = self.world * self.MAILBOX_BYTES  # mailboxes first
         self._stage_bytes = min(16 << 20, heap_bytes // 8)
@@ -222,7 +223,8 @@ class SymmComm:
         _native.check(self.lib.b200rnn_comm_status(C.byref(self.ctx), C.byref(st), self._sp()), "comm_status")
         if st.value != 0:
             missing = [r for r in range(self.world) if st.value & (1 << r)]
-            raise RuntimeError(f"rank {self.rank}: comm watchdog fired, no signal from rank(s) {missing}")
+            extra = " (local grid barrier timed out)" if st.value & (1 << 30) else ""
+            raise RuntimeError(f"rank {self.rank}: comm watchdog fired, no signal from rank(s) {missing}{extra}")
 
     def set_delay_ns(self, ns: int) -> None:
         self.ctx.delay_ns = int(ns)
