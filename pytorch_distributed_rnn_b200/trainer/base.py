@@ -18,6 +18,7 @@ loop runs plain torch autograd — the plumbing/oracle configuration.
 from __future__ import annotations
 
 import logging
+import os
 import resource
 import time
 from pathlib import Path
@@ -30,6 +31,23 @@ from ..data.sampler import ShardedEpochSampler
 from ..ops.optim import FusedAdam
 from ..utils.arena import ParamArena
 from .formatter import TrainingMessageFormatter
+
+
+class _Range:
+    """NVTX range when B200RNN_NVTX=1 (for nsys / ncu timelines); free otherwise.  The reference has
+    no tracing beyond a wall clock and memory_profiler."""
+    on = os.environ.get("B200RNN_NVTX", "0") == "1"
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        if self.on and torch.cuda.is_available():
+            torch.cuda.nvtx.range_push(self.name)
+
+    def __exit__(self, *a):
+        if self.on and torch.cuda.is_available():
+            torch.cuda.nvtx.range_pop()
 
 
 def peak_rss_mib() -> float:
@@ -129,10 +147,12 @@ class Trainer:
             if self.sampler is not None:
                 self.sampler.set_epoch(epoch)
             logging.info(formatter.epoch_start_message(epoch))
-            train_loss, _ = self._train_step(formatter)
+            with _Range(f"epoch{epoch}/train"):
+                train_loss, _ = self._train_step(formatter)
             training_history.append(train_loss)
             if self.validation_set is not None:
-                validation_loss, _ = self._evaluate(self.validation_set, formatter, epoch)
+                with _Range(f"epoch{epoch}/validate"):
+                    validation_loss, _ = self._evaluate(self.validation_set, formatter, epoch)
                 validation_history.append(validation_loss)
                 if best_loss is None or best_loss > validation_loss:
                     logging.info(f"New best model in epoch {epoch + 1}")
