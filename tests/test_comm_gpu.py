@@ -157,3 +157,56 @@ def test_gpu_parameter_server_one_sided(tmp_path):
     for r in (1, 2):
         losses = [float(m) for m in re.findall(r"Loss: ([\d.]+)", outs[r][1])]
         assert len(losses) == 4 and losses[-1] < losses[0], losses   # 2 epochs x 128/64 batches, learning
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_cli_trainers_on_gpus_world_size_invariance(tmp_path):
+    """`local` on 1 GPU vs `distributed` / `horovod` on 2 GPUs through the CLI: same mean step loss and
+    summed correct count, performance line per rank, DDP checkpoint prefix."""
+    import os
+    import re
+    from pytorch_distributed_rnn_b200.data import synthetic
+    from pytorch_distributed_rnn_b200.parallel.launch import launch
+    ds = tmp_path / "ds"
+    synthetic.write_dataset(ds, train=960, valid=40, test=40)
+    step_re = re.compile(r"Rank: (\d+)   Train Batch: (\d+)/(\d+) .*Loss: ([\d.]+)\tAcc: (\d+)/(\d+)")
+
+    def run(n, trainer, extra=()):
+        cmd = [sys.executable, "-m", "pytorch_distributed_rnn_b200", "--dataset-path", str(ds), "--epochs", "1",
+               "--batch-size", "480", "--seed", "123456789", "--checkpoint-directory", str(tmp_path / f"ck_{trainer}"),
+               "--history-path", str(tmp_path / f"h_{trainer}.json"), *extra, trainer]
+        res = launch(cmd, n, timeout=300, env={"PYTHONPATH": str(ROOT)})
+        steps = {}
+        for r, cp in enumerate(res):
+            assert cp.returncode == 0, f"{trainer} rank {r}:\n{cp.stdout[-1500:]}\n{cp.stderr[-3000:]}"
+            for m in step_re.finditer(cp.stderr):
+                steps.setdefault(int(m[2]), []).append((float(m[4]), int(m[5]), int(m[6])))
+        return res, steps
+
+    _, local = run(1, "local", ["--no-validation"])
+    assert len(local) == 2
+    for trainer in ("distributed", "horovod"):
+        res, two = run(2, trainer)
+        for b, ((l, c, n),) in local.items():
+            assert len(two[b]) == 2
+            assert abs(sum(x[0] for x in two[b]) / 2 - l) < 5e-6 and sum(x[1] for x in two[b]) == c and sum(x[2] for x in two[b]) == n
+        assert all(f"{r}: Memory Usage:" in res[r].stderr for r in range(2))
+        assert "Evaluation Epoch: 1/1" in res[0].stderr and "Test Evaluation" in res[0].stderr
+        ck = torch.load(tmp_path / f"ck_{trainer}" / "best-model.pt", weights_only=False)
+        assert all(k.startswith("module.") for k in ck["model_state"]) == (trainer == "distributed")
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_toy_examples_on_gpus():
+    from pytorch_distributed_rnn_b200.parallel.launch import launch
+    for script in ("example_ddp.py", "example_horovod.py", "example_distributed.py"):
+        res = launch([sys.executable, str(ROOT / "examples" / script)], 2, timeout=300)
+        for r, cp in enumerate(res):
+            assert cp.returncode == 0, f"{script} rank {r}:\n{cp.stdout[-1500:]}\n{cp.stderr[-3000:]}"
+        if script != "example_distributed.py":
+            finals = [[l for l in cp.stdout.splitlines() if "parameters:" in l][-1].split("parameters:")[1] for cp in res]
+            assert finals[0] == finals[1], (script, finals)
+        else:
+            assert all(f"Rank  {r}  has data  1.0" in res[r].stdout for r in range(2))
