@@ -97,7 +97,7 @@ __device__ __forceinline__ void group_transpose_reduce(float (&s)[KQ][4], int kq
 // ---------------------------------------------------------------------------
 // Forward, one layer.  vs = [2][BTMAX][VS_LD] operand staging (double buffered).
 // ---------------------------------------------------------------------------
-template <int H, int KQ, int KPT, int NG>
+template <int H, int KQ, int KPT, int NG, int LS>
 __device__ __forceinline__ void fwd_layer(
     const float* inp /* may be h_seq of the layer below, written earlier by this CTA: no __restrict__ */,
     int64_t in_sb, int64_t in_st, int in_dim,
@@ -179,8 +179,9 @@ __device__ __forceinline__ void fwd_layer(
         const int b = g * KQ + si;
         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
         const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + vcol<KPT>(kq * KPT)]);
+        const bool live = (g < NG - 1) || (si < LS);   // compile-time: the tile holds (NG-1)*KQ + LS samples
 #pragma unroll
-        for (int j4 = 0; j4 < KPT / 4; ++j4) {
+        for (int j4 = 0; j4 < (live ? KPT / 4 : 0); ++j4) {
           const float4 v = vp[j4];
           a0 = fmaf(w[0][4 * j4 + 0], v.x, a0); a1 = fmaf(w[1][4 * j4 + 0], v.x, a1);
           a2 = fmaf(w[2][4 * j4 + 0], v.x, a2); a3 = fmaf(w[3][4 * j4 + 0], v.x, a3);
@@ -220,7 +221,7 @@ __device__ __forceinline__ void fwd_layer(
   }
 }
 
-template <int H, int KQ, int KPT0, int NG>
+template <int H, int KQ, int KPT0, int NG, int LS>
 __global__ void __launch_bounds__(H* KQ) lstm_fwd_kernel(const FwdArgs a) {
   constexpr int KPT1 = 2 * H / KQ;
   constexpr int BTMAX = NG * KQ;
@@ -230,19 +231,23 @@ __global__ void __launch_bounds__(H* KQ) lstm_fwd_kernel(const FwdArgs a) {
   const int BTc = min(a.BT, a.B - b0);
   if (BTc <= 0) return;
   const int64_t lsz = (int64_t)a.T * a.B * H;
-  fwd_layer<H, KQ, KPT0, NG>(a.x, (int64_t)a.T * a.I, a.I, a.I,
+  fwd_layer<H, KQ, KPT0, NG, LS>(a.x, (int64_t)a.T * a.I, a.I, a.I,
                              a.params + a.off_wih[0], a.params + a.off_whh[0],
                              a.params + a.off_bih[0], a.params + a.off_bhh[0],
                              a.h_seq, a.c_seq, a.g_seq, a.T, a.B, b0, BTc, a.training, vs);
   for (int l = 1; l < a.L; ++l) {
     __syncthreads();  // layer l-1's h_seq tile (written by this CTA) is now visible
-    fwd_layer<H, KQ, KPT1, NG>(a.h_seq + (l - 1) * lsz, H, (int64_t)a.B * H, H,
+    fwd_layer<H, KQ, KPT1, NG, LS>(a.h_seq + (l - 1) * lsz, H, (int64_t)a.B * H, H,
                                a.params + a.off_wih[l], a.params + a.off_whh[l],
                                a.params + a.off_bih[l], a.params + a.off_bhh[l],
                                a.h_seq + l * lsz, a.c_seq + l * lsz, a.g_seq + 4 * l * lsz,
                                a.T, a.B, b0, BTc, a.training, vs);
   }
 }
+
+// Per-phase clock64 stamps of one backward step (profiling aid, read with b200rnn_bwd_prof()).
+__device__ long long g_bwd_prof[2][8];
+#define BWD_STAMP(role, i) do { if (stamp) g_bwd_prof[role][i] = clock64(); } while (0)
 
 // ---------------------------------------------------------------------------
 // Backward, one layer.  Warp-specialised: the CTA has 2*NT threads.
@@ -253,7 +258,7 @@ __global__ void __launch_bounds__(H* KQ) lstm_fwd_kernel(const FwdArgs a) {
 //           layer below), plus the prefetch/staging of the next step's operands.
 // B1 and B2 run concurrently on different warps; two __syncthreads per step.
 // ---------------------------------------------------------------------------
-template <int H, int KQ, int KPT, int NG, bool HAS_DX>
+template <int H, int KQ, int KPT, int NG, int BTU, bool HAS_DX>
 __device__ __forceinline__ void bwd_layer(
     const float* __restrict__ inp, int64_t in_sb, int64_t in_st, int in_dim,
     const float* __restrict__ w_ih, const float* __restrict__ w_hh,
@@ -278,6 +283,7 @@ __device__ __forceinline__ void bwd_layer(
   constexpr int NPFX = (BTMAX * INP + NT - 1) / NT;
   constexpr int NPFH = (BTMAX * H + NT - 1) / NT;
   static_assert(NT % NOUT == 0 && JQ >= 1 && (JQ & (JQ - 1)) == 0 && JR % 4 == 0, "bad B mapping");
+  static_assert(BTU <= BTMAX && BTU > BTMAX - KQ, "BTU must fall in the last sample group");
   static_assert(!HAS_DX || INP == H, "dx only for stacked layers (input width == H)");
 
   // all rows of the staging buffers start at zero: the sample loops below are compile-time (BTMAX
@@ -333,33 +339,36 @@ __device__ __forceinline__ void bwd_layer(
 
     for (int t = T - 1; t >= 0; --t) {
       const int cur = t & 1;
+      const bool stamp = HAS_DX && t == T / 2 && blockIdx.x == 0 && threadIdx.x == 0;
+      BWD_STAMP(0, 0);
       float4 gv[NG]; float cprev[NG], da[NG];
 #pragma unroll
       for (int g = 0; g < NG; ++g) { gv[g] = pf_g[g]; cprev[g] = pf_cprev[g]; da[g] = pf_da[g]; }
       if (t > 0) load_step(t - 1);
-      // ---- phase A: gate gradients for my (sample, unit) slots ----
+      // ---- phase A: gate gradients for my (sample, unit) slots, branch-free so the NG slots'
+      // MUFU / FMA chains interleave (slots past the tile end see zero inputs and produce zeros) ----
 #pragma unroll
       for (int g = 0; g < NG; ++g) {
         const int b = g * KQ + kq;
-        if (b < BTc) {
-          const float ig = gv[g].x, fg = gv[g].y, gg = gv[g].z, og = gv[g].w;
-          const float dh = dhrec_s[b * H + u] + da[g];
-          const float tc = tanh_f(c_t[g]);
-          const float dct = fmaf(dh * og, 1.0f - tc * tc, dc_reg[g]);
-          const float dpi = dct * gg * ig * (1.0f - ig);
-          const float dpf = dct * cprev[g] * fg * (1.0f - fg);
-          const float dpg = dct * ig * (1.0f - gg * gg);
-          const float dpo = dh * tc * og * (1.0f - og);
-          dc_reg[g] = dct * fg;
-          c_t[g] = cprev[g];
-          *reinterpret_cast<float4*>(&dG_s[b * DG_LD + dgcol<JR>(u * 4)]) = make_float4(dpi, dpf, dpg, dpo);
-          dbacc[0] += dpi; dbacc[1] += dpf; dbacc[2] += dpg; dbacc[3] += dpo;
-        }
+        const float ig = gv[g].x, fg = gv[g].y, gg = gv[g].z, og = gv[g].w;
+        const float dh = dhrec_s[b * H + u] + da[g];
+        const float tc = tanh_f(c_t[g]);
+        const float dct = fmaf(dh * og, 1.0f - tc * tc, dc_reg[g]);
+        const float dpi = dct * gg * ig * (1.0f - ig);
+        const float dpf = dct * cprev[g] * fg * (1.0f - fg);
+        const float dpg = dct * ig * (1.0f - gg * gg);
+        const float dpo = dh * tc * og * (1.0f - og);
+        dc_reg[g] = dct * fg;
+        c_t[g] = cprev[g];
+        *reinterpret_cast<float4*>(&dG_s[b * DG_LD + dgcol<JR>(u * 4)]) = make_float4(dpi, dpf, dpg, dpo);
+        dbacc[0] += dpi; dbacc[1] += dpf; dbacc[2] += dpg; dbacc[3] += dpo;
       }
+      BWD_STAMP(0, 1);
       __syncthreads();  // (S1) dG_s complete
+      BWD_STAMP(0, 2);
       // ---- phase B2: dW += dG^T [x_t | h_{t-1}] ----
 #pragma unroll
-      for (int b = 0; b < BTMAX; ++b) {
+      for (int b = 0; b < BTU; ++b) {
         const float4 d = *reinterpret_cast<const float4*>(&dG_s[b * DG_LD + dgcol<JR>(u * 4)]);
         const float4* vp = reinterpret_cast<const float4*>(&vs[(cur * BTMAX + b) * VS_LD + vcol<KPT>(kq * KPT)]);
 #pragma unroll
@@ -375,7 +384,9 @@ __device__ __forceinline__ void bwd_layer(
           dW[3][4 * j4 + 2] = fmaf(d.w, v.z, dW[3][4 * j4 + 2]); dW[3][4 * j4 + 3] = fmaf(d.w, v.w, dW[3][4 * j4 + 3]);
         }
       }
+      BWD_STAMP(0, 3);
       __syncthreads();  // (S2) dhrec_s / next operands ready (role B); dG_s, vs[cur] free
+      BWD_STAMP(0, 4);
     }
     // ---- emit this CTA's partial gradients (torch parameter layout) ----
 #pragma unroll
@@ -444,14 +455,18 @@ __device__ __forceinline__ void bwd_layer(
 
     for (int t = T - 1; t >= 0; --t) {
       const int nxt = (t & 1) ^ 1;
+      const bool stamp = HAS_DX && t == T / 2 && blockIdx.x == 0 && threadIdx.x == NT;
+      BWD_STAMP(1, 0);
       if (t > 0) load_operands(t - 1);   // global loads in flight across the barrier
+      BWD_STAMP(1, 1);
       __syncthreads();  // (S1) dG_s complete
+      BWD_STAMP(1, 2);
       // ---- phase B1: dv = dG x [W_ih | W_hh]  (dx for the layer below, dh for step t-1) ----
       // all dot products first (BTMAX x 4 independent FMA chains, loads hoistable), then the
       // lane reductions back to back, then the stores
-      float res[BTMAX];
+      float res[BTU];
 #pragma unroll
-      for (int b = 0; b < BTMAX; ++b) {
+      for (int b = 0; b < BTU; ++b) {
         const float4* dp = reinterpret_cast<const float4*>(&dG_s[b * DG_LD + jq * (JR + 4)]);
         float acc0 = 0.0f, acc1 = 0.0f, acc2 = 0.0f, acc3 = 0.0f;
 #pragma unroll
@@ -463,24 +478,27 @@ __device__ __forceinline__ void bwd_layer(
         res[b] = (acc0 + acc1) + (acc2 + acc3);
       }
 #pragma unroll
-      for (int b = 0; b < BTMAX; ++b) res[b] = group_sum<JQ>(res[b]);
+      for (int b = 0; b < BTU; ++b) res[b] = group_sum<JQ>(res[b]);
       if (jq == 0) {
         const int kk = KOFF + kB;
 #pragma unroll
-        for (int b = 0; b < BTMAX; ++b) {
+        for (int b = 0; b < BTU; ++b) {
           if (b < BTc) {
             if (HAS_DX && kk < INP) dx_out[((int64_t)t * B + (b0 + b)) * H + kk] = res[b];
             else dhrec_s[b * H + (kk - INP)] = res[b];
           }
         }
       }
+      BWD_STAMP(1, 3);
       if (t > 0) store_operands(nxt);
+      BWD_STAMP(1, 4);
       __syncthreads();  // (S2)
+      BWD_STAMP(1, 5);
     }
   }
 }
 
-template <int H, int KQ, int KPT0, int NG>
+template <int H, int KQ, int KPT0, int NG, int BTU>
 __global__ void __launch_bounds__(2 * H * KQ, 1) lstm_bwd_kernel(const BwdArgs a) {
   constexpr int NT2 = 2 * H * KQ;   // all threads (both roles)
   constexpr int KPT1 = 2 * H / KQ;
@@ -500,6 +518,9 @@ __global__ void __launch_bounds__(2 * H * KQ, 1) lstm_bwd_kernel(const BwdArgs a
   float* row = a.rows + (int64_t)blockIdx.x * a.row_floats;
   const int64_t lsz = (int64_t)a.T * a.B * H;
   const int L = a.L;
+  // rows past the tile end must hold finite values: phase A is branch-free
+  for (int idx = tid; idx < BTMAX * H; idx += NT2) dhrec_s[idx] = 0.0f;
+  __syncthreads();
 
   // ---- top of the network: fused head + CE, or external d_hn ----
   const bool fused_head = (a.labels != nullptr && a.C > 0);
@@ -575,7 +596,7 @@ __global__ void __launch_bounds__(2 * H * KQ, 1) lstm_bwd_kernel(const BwdArgs a
     const float* dabove; int64_t da_sb, da_st;
     if (l == L - 1) { dabove = a.d_out; da_sb = (int64_t)a.T * H; da_st = H; }
     else { dabove = a.dxbuf + ((l + 1) & 1) * lsz; da_sb = H; da_st = (int64_t)a.B * H; }
-    bwd_layer<H, KQ, KPT1, NG, true>(
+    bwd_layer<H, KQ, KPT1, NG, BTU, true>(
         a.h_seq + (l - 1) * lsz, H, (int64_t)a.B * H, H,
         a.params + a.off_wih[l], a.params + a.off_whh[l],
         a.h_seq + l * lsz, a.c_seq + l * lsz, a.g_seq + 4 * l * lsz,
@@ -592,7 +613,7 @@ __global__ void __launch_bounds__(2 * H * KQ, 1) lstm_bwd_kernel(const BwdArgs a
     const float* dabove; int64_t da_sb, da_st;
     if (L == 1) { dabove = a.d_out; da_sb = (int64_t)a.T * H; da_st = H; }
     else { dabove = a.dxbuf + (1 & 1) * lsz; da_sb = H; da_st = (int64_t)a.B * H; }
-    bwd_layer<H, KQ, KPT0, NG, false>(
+    bwd_layer<H, KQ, KPT0, NG, BTU, false>(
         a.x, (int64_t)a.T * a.I, a.I, a.I,
         a.params + a.off_wih[0], a.params + a.off_whh[0],
         a.h_seq, a.c_seq, a.g_seq,
@@ -608,18 +629,25 @@ __global__ void __launch_bounds__(2 * H * KQ, 1) lstm_bwd_kernel(const BwdArgs a
 // ---------------------------------------------------------------------------
 constexpr int kH = 32, kKQ = 4;
 
-// Rows per CTA.  Forward tiles are multiples of KQ (its sample groups are KQ wide and computed
-// branch-free); pick the tile that minimises the per-SM load when CTAs spread evenly with at most
+// Rows per CTA (any size 1..16; kernels are instantiated per (groups, live samples in the last group));
+// pick the tile that minimises the per-SM load when CTAs spread evenly with at most
 // `slots` co-resident CTAs per SM (register-limited), smaller tile on ties (more warps per SM).
 int choose_bt_fwd(int B) {
+  // Measured (tools/kernel_bench.py): a forward step costs about one unit per SAMPLE GROUP resident on
+  // the SM (reduce + activation + barrier overhead) plus ~6% of that per live sample, so partially
+  // filled groups are only worth it when the whole tile is a single group.
   const int sms = num_sms(), slots = 4;
-  int best = 4, best_load = 1 << 30;
-  for (int bt = 4; bt <= kMaxBT; bt += 4) {
+  const int cand[7] = {1, 2, 3, 4, 8, 12, 16};
+  int best = 4;
+  float best_cost = 1e30f;
+  for (int i = 0; i < 7; ++i) {
+    const int bt = cand[i];
     const int n = (B + bt - 1) / bt;
     const int per_sm = (n + sms - 1) / sms;
     const int waves = (per_sm + slots - 1) / slots;
-    const int load = waves * slots >= per_sm && waves == 1 ? per_sm * bt : waves * slots * bt;
-    if (load < best_load) { best_load = load; best = bt; }
+    const int resident = waves == 1 ? per_sm : waves * slots;
+    const float cost = resident * ((bt + kKQ - 1) / kKQ + 0.06f * bt);
+    if (cost < best_cost) { best_cost = cost; best = bt; }
   }
   return best;
 }
@@ -628,7 +656,9 @@ int choose_bt_fwd(int B) {
 int choose_bt(int B) {
   const int sms = num_sms();
   int best = 4, best_load = 1 << 30;
-  for (int bt = 4; bt <= kMaxBT; bt += 4) {
+  const int cand[10] = {1, 2, 3, 4, 5, 6, 8, 10, 12, 16};   // instantiated tile sizes
+  for (int i = 0; i < 10; ++i) {
+    const int bt = cand[i];
     const int n = (B + bt - 1) / bt;
     const int load = ((n + sms - 1) / sms) * bt;
     if (load <= best_load) { best_load = load; best = bt; }   // ties: larger tile = a single wave
@@ -642,17 +672,28 @@ bool small_supported(const b200rnn_model_desc* d) {
          d->num_classes >= 0 && d->num_classes <= 32 && d->seq_len >= 1 && d->batch >= 1;
 }
 
-template <int KPT0, int NG>
+template <int KPT0, int NG, int LS>
 int launch_fwd(const FwdArgs& a, int n_cta, cudaStream_t s) {
-  lstm_fwd_kernel<kH, kKQ, KPT0, NG><<<n_cta, kH * kKQ, 0, s>>>(a);
+  lstm_fwd_kernel<kH, kKQ, KPT0, NG, LS><<<n_cta, kH * kKQ, 0, s>>>(a);
   B200_CHECK_LAUNCH();
   return B200RNN_OK;
 }
-template <int KPT0, int NG>
+template <int KPT0, int NG, int BTU = 4 * NG>
 int launch_bwd(const BwdArgs& a, int n_cta, cudaStream_t s) {
-  lstm_bwd_kernel<kH, kKQ, KPT0, NG><<<n_cta, 2 * kH * kKQ, 0, s>>>(a);
+  lstm_bwd_kernel<kH, kKQ, KPT0, NG, BTU><<<n_cta, 2 * kH * kKQ, 0, s>>>(a);
   B200_CHECK_LAUNCH();
   return B200RNN_OK;
+}
+// tile size -> instantiation (sample groups NG = ceil(BT / 4), compile-time sample count BT)
+int dispatch_bwd(const BwdArgs& a, int n_cta, bool narrow, cudaStream_t s) {
+#define B200_BWD_CASE(BT, NG) case BT: return narrow ? launch_bwd<12, NG, BT>(a, n_cta, s) : launch_bwd<16, NG, BT>(a, n_cta, s);
+  switch (a.BT) {
+    B200_BWD_CASE(1, 1) B200_BWD_CASE(2, 1) B200_BWD_CASE(3, 1) B200_BWD_CASE(4, 1) B200_BWD_CASE(5, 2)
+    B200_BWD_CASE(6, 2) B200_BWD_CASE(8, 2) B200_BWD_CASE(10, 3) B200_BWD_CASE(12, 3) B200_BWD_CASE(16, 4)
+  }
+#undef B200_BWD_CASE
+  set_error("lstm_bwd: no kernel instantiated for a tile of %d rows", a.BT);
+  return B200RNN_EINVAL;
 }
 
 }  // namespace
@@ -708,11 +749,14 @@ extern "C" int b200rnn_lstm_fwd(const b200rnn_model_desc* d, const float* params
   const int ng = (a.BT + kKQ - 1) / kKQ;
   cudaStream_t s = (cudaStream_t)stream;
   const bool narrow = d->input_size <= 16;
+  const int ls = a.BT - (ng - 1) * kKQ;
+#define B200_FWD_LS(NG, LS) case LS: return narrow ? launch_fwd<12, NG, LS>(a, n_cta, s) : launch_fwd<16, NG, LS>(a, n_cta, s);
 #define B200_DISPATCH_FWD(NG)                                                     \
-  case NG: return narrow ? launch_fwd<12, NG>(a, n_cta, s) : launch_fwd<16, NG>(a, n_cta, s);
+  case NG: switch (ls) { B200_FWD_LS(NG, 1) B200_FWD_LS(NG, 2) B200_FWD_LS(NG, 3) B200_FWD_LS(NG, 4) } break;
   switch (ng) {
     B200_DISPATCH_FWD(1) B200_DISPATCH_FWD(2) B200_DISPATCH_FWD(3) B200_DISPATCH_FWD(4)
   }
+#undef B200_FWD_LS
 #undef B200_DISPATCH_FWD
   set_error("lstm_fwd: internal tiling error (ng=%d)", ng);
   return B200RNN_EINVAL;
@@ -747,15 +791,9 @@ extern "C" int b200rnn_lstm_bwd(const b200rnn_model_desc* d, const float* params
   const int ng = (a.BT + kKQ - 1) / kKQ;
   cudaStream_t s = (cudaStream_t)stream;
   const bool narrow = d->input_size <= 16;
-#define B200_DISPATCH_BWD(NG)                                                     \
-  case NG: return narrow ? launch_bwd<12, NG>(a, n_cta, s) : launch_bwd<16, NG>(a, n_cta, s);
-  switch (ng) {
-    B200_DISPATCH_BWD(1) B200_DISPATCH_BWD(2) B200_DISPATCH_BWD(3) B200_DISPATCH_BWD(4)
-  }
-#undef B200_DISPATCH_BWD
-  set_error("lstm_bwd: internal tiling error (ng=%d)", ng);
-  return B200RNN_EINVAL;
+  return dispatch_bwd(a, n_cta, narrow, s);
 }
+
 
 // ---------------------------------------------------------------------------
 // Allocation-free backward (see include/b200rnn.h: b200rnn_lstm_bwd_static).
@@ -835,15 +873,14 @@ extern "C" int b200rnn_lstm_bwd_static(const b200rnn_model_desc* d, const float*
   const int ng = (a.BT + kKQ - 1) / kKQ;
   cudaStream_t s = (cudaStream_t)stream;
   const bool narrow = d->input_size <= 16;
-  rc = B200RNN_EINVAL;
-  switch (ng) {
-    case 1: rc = narrow ? launch_bwd<12, 1>(a, n_cta, s) : launch_bwd<16, 1>(a, n_cta, s); break;
-    case 2: rc = narrow ? launch_bwd<12, 2>(a, n_cta, s) : launch_bwd<16, 2>(a, n_cta, s); break;
-    case 3: rc = narrow ? launch_bwd<12, 3>(a, n_cta, s) : launch_bwd<16, 3>(a, n_cta, s); break;
-    case 4: rc = narrow ? launch_bwd<12, 4>(a, n_cta, s) : launch_bwd<16, 4>(a, n_cta, s); break;
-    default: set_error("lstm_bwd_static: internal tiling error (ng=%d)", ng); break;
-  }
+  rc = dispatch_bwd(a, n_cta, narrow, s);
   if (rc != B200RNN_OK) return rc;
   // fixed-order sum of the rows into the caller's gradient vector (a kernel launch, no allocation)
   return b200rnn_reduce_rows(scratch, n_cta, a.row_floats, grad_out, 0, stream);
+}
+
+extern "C" int b200rnn_bwd_prof(long long* out16) {
+  B200_REQUIRE(out16 != nullptr, B200RNN_EINVAL, "bwd_prof: null");
+  B200_CHECK_CUDA(cudaMemcpyFromSymbol(out16, g_bwd_prof, sizeof(long long) * 16));
+  return B200RNN_OK;
 }
