@@ -166,6 +166,9 @@ class Trainer:
             self.last_device_seconds = ev0.elapsed_time(ev1) / 1e3
         duration = time.perf_counter() - start
         self.last_duration = duration
+        comm = self._get_comm()
+        if comm is not None and hasattr(comm, "check"):
+            comm.check()   # surface a fired comm watchdog (dead / stuck peer) instead of training on garbage
         logging.info(formatter.performance_message(peak_rss_mib(), duration))
         if cuda:
             logging.info("Rank: {:02d}   Device time: {:.6f} s, peak device memory: {:.1f} MiB".format(
