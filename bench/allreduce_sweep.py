@@ -66,7 +66,7 @@ def main():
     info = pg.init_distributed()
     rank, world, dev = info.rank, info.world_size, info.device
     max_floats = a.max_bytes // 4
-    comm = SymmComm(info, inbox_floats=max_floats, heap_bytes=a.max_bytes + (64 << 20), max_blocks=1 << 18)
+    comm = SymmComm(info, inbox_floats=max_floats, heap_bytes=2 * a.max_bytes + (64 << 20), max_blocks=1 << 18)
     lib = _native.lib()
     results = []
     sizes = []
@@ -85,7 +85,9 @@ def main():
             rows = torch.ones(1, n + 2, device=dev)
             slot = torch.zeros(2, device=dev)
             row = {"bytes": nbytes, "world": world, "delay_us": delay}
-            for algo, name in ((1, "oneshot"), (2, "twoshot")):
+            for algo, name in ((1, "oneshot"), (2, "twoshot"), (3, "nvls")):
+                if algo == 3 and comm.mc_base is None:
+                    continue
                 if algo == 1 and (n + 1023) // 1024 > comm.ctx.max_blocks:
                     continue
                 comm.algo = algo
@@ -102,7 +104,7 @@ def main():
             per_rank_two = 2 * (world - 1) / world * nbytes
             row["roofline_oneshot_us"] = per_rank_one / (NVLINK_GBS * 1e3)
             row["roofline_twoshot_us"] = per_rank_two / (NVLINK_GBS * 1e3)
-            for name in ("oneshot", "twoshot", "nccl"):
+            for name in ("oneshot", "twoshot", "nvls", "nccl"):
                 if f"{name}_us" in row:
                     roof = row["roofline_oneshot_us"] if name == "oneshot" else row["roofline_twoshot_us"]
                     row[f"{name}_frac_of_nvlink_roofline"] = roof / row[f"{name}_us"] if row[f"{name}_us"] > 0 else None

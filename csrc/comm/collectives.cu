@@ -272,6 +272,106 @@ __global__ void __launch_bounds__(kThreads) twoshot_kernel(
   if (blockIdx.x == 0 && threadIdx.x < c.world) wait_flag(c, flags_pr(c, c.rank, threadIdx.x), seq, threadIdx.x);
 }
 
+// ---------------------------------------------------------------------------
+// NVLS: the reduction happens INSIDE the NVSwitch.  Every rank writes its (row-reduced) gradient into
+// the same heap slot of its own region; after a cross-rank barrier the owner of shard p issues
+// multimem.ld_reduce on the MULTICAST address of that slot (the switch returns the sum over all ranks
+// in one load), runs the optimizer on its shard and multimem.st's the updated parameters, which the
+// switch replicates into every rank's arena.  Per-GPU NVLink traffic ~ n instead of 2(W-1)/W * n * ...
+// and no inboxes.  Needs a region created by b200rnn_symm_vmm_create with multicast.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc_ptr) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc_ptr) : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st(float* mc_ptr, const float4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+               ::"l"(mc_ptr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// all-to-all flag barrier between the ranks (block 0 signals, every block's first W threads wait)
+__device__ __forceinline__ void rank_barrier(const Ctx& c, uint32_t seq, bool use_pr) {
+  if (blockIdx.x == 0 && threadIdx.x < c.world) {
+    __threadfence_system();
+    uint32_t* f = use_pr ? flags_pr(c, threadIdx.x, c.rank) : flags_ar(c, threadIdx.x, c.rank, 0);
+    st_release_sys(f, seq);
+  }
+  if (threadIdx.x < c.world) {
+    const uint32_t* f = use_pr ? flags_pr(c, c.rank, threadIdx.x) : flags_ar(c, c.rank, threadIdx.x, 0);
+    wait_flag(c, f, seq, threadIdx.x);
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kThreads) nvls_update_kernel(
+    Ctx c, char* mc_base, uint32_t seq, unsigned int sync_target, const float* __restrict__ rows, int n_rows, long long n,
+    long long row_stride, float* buf, long long buf_heap_off, long long grad_heap_off, float* __restrict__ exp_avg,
+    float* __restrict__ exp_avg_sq, OptScalars o, float* __restrict__ metrics, long long shard) {
+  unsigned int* counter = reinterpret_cast<unsigned int*>(c.base[c.rank] + c.off_flags_bar) + 2 * B200RNN_MAX_PEERS + 1;
+  const long long tstride = (long long)gridDim.x * kThreads * kElems;
+  const long long t0 = ((long long)blockIdx.x * kThreads + threadIdx.x) * kElems;
+  const long long n4 = (n + 3) & ~3LL;
+  if (blockIdx.x == 0 && threadIdx.x < 2 && metrics != nullptr) {
+    float g = 0.0f;
+    for (int r = 0; r < n_rows; ++r) g += rows[(long long)r * row_stride + n + threadIdx.x];
+    metrics[threadIdx.x] = g;
+  }
+  // ---- phase 0: my row-reduced gradient -> my copy of the shared slot (zero padded to n4) ----
+  float* slot = reinterpret_cast<float*>(c.base[c.rank] + c.off_heap + grad_heap_off);
+  for (long long i = t0; i < n4; i += tstride) {
+    const F4 g = reduce_rows4(rows, n_rows, row_stride, i, n);
+    *reinterpret_cast<float4*>(slot + i) = make_float4(g.v[0], g.v[1], g.v[2], g.v[3]);
+  }
+  asm volatile("fence.proxy.alias;" ::: "memory");
+  grid_sync(c, counter, sync_target - gridDim.x);
+  if (blockIdx.x == 0 && threadIdx.x == 0) delay(c);
+  rank_barrier(c, seq, false);
+  asm volatile("fence.proxy.alias;" ::: "memory");
+  // ---- phase 1: my shard: in-switch reduction, optimizer, in-switch broadcast of the parameters ----
+  {
+    const long long lo = (long long)c.rank * shard;
+    const long long hi = lo + shard < n4 ? lo + shard : n4;
+    const float* mc_grad = reinterpret_cast<const float*>(mc_base + c.off_heap + grad_heap_off);
+    float* mc_par = reinterpret_cast<float*>(mc_base + c.off_heap + buf_heap_off);
+    constexpr int U = 4;   // in-switch loads in flight per thread
+    for (long long i0 = lo + t0; i0 < hi; i0 += U * tstride) {
+      float4 s4[U];
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        const long long i = i0 + k * tstride;
+        if (i < hi) s4[k] = multimem_ld_reduce_add(mc_grad + i);
+      }
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        const long long i = i0 + k * tstride;
+        if (i >= hi) break;
+        const float sv[4] = {s4[k].x, s4[k].y, s4[k].z, s4[k].w};
+        float out[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const long long j = i + e;
+          float p = 0.0f;
+          if (j < n) {
+            p = buf[j];
+            float m = exp_avg ? exp_avg[j] : 0.0f;
+            float v = exp_avg_sq ? exp_avg_sq[j] : 0.0f;
+            apply_update(o, sv[e] * o.grad_scale, p, m, v);
+            if (exp_avg) exp_avg[j] = m;
+            if (exp_avg_sq) exp_avg_sq[j] = v;
+          }
+          out[e] = p;
+        }
+        multimem_st(mc_par + i, make_float4(out[0], out[1], out[2], out[3]));
+      }
+    }
+  }
+  asm volatile("fence.proxy.alias;" ::: "memory");
+  grid_sync(c, counter, sync_target);
+  rank_barrier(c, seq, true);
+  asm volatile("fence.proxy.alias;" ::: "memory");
+}
+
 // K8 broadcast on the symmetric heap: root copies its bytes into every peer's heap, then flags.
 __global__ void __launch_bounds__(kThreads) broadcast_kernel(Ctx c, uint32_t seq, long long heap_off, long long n16,
                                                               long long tail_bytes, int root) {
@@ -559,5 +659,34 @@ extern "C" int b200rnn_comm_ps_pull(const b200rnn_comm_ctx* ctx, int32_t server,
 extern "C" int b200rnn_comm_forget(const void* region_base) {
   for (int i = 0; i < g_sync_n; ++i)
     if (g_sync[i].base == region_base) { g_sync[i] = g_sync[g_sync_n - 1]; --g_sync_n; break; }
+  return B200RNN_OK;
+}
+
+extern "C" int b200rnn_comm_allreduce_update_nvls(const b200rnn_comm_ctx* ctx, void* mc_base, uint32_t seq, const float* rows,
+                                                  int32_t n_rows, int64_t n_params, float* params, int64_t params_heap_off,
+                                                  int64_t grad_heap_off, float* exp_avg, float* exp_avg_sq,
+                                                  const b200rnn_optim_desc* opt, float* metrics, void* stream) {
+  int rc = check_ctx(ctx, "comm_allreduce_update_nvls");
+  if (rc) return rc;
+  B200_REQUIRE(mc_base && rows && params && opt && n_rows >= 1 && n_params > 0, B200RNN_EINVAL, "comm_allreduce_update_nvls: bad argument");
+  const int64_t n4 = (n_params + 3) & ~int64_t(3);
+  B200_REQUIRE(params_heap_off >= 0 && grad_heap_off >= 0 && (params_heap_off & 15) == 0 && (grad_heap_off & 15) == 0 &&
+               params_heap_off + n4 * 4 <= ctx->heap_bytes && grad_heap_off + n4 * 4 <= ctx->heap_bytes, B200RNN_EINVAL,
+               "comm_allreduce_update_nvls: parameter arena and gradient slot must live 16-byte aligned in the symmetric heap");
+  B200_REQUIRE(opt->kind != 0 || (exp_avg && exp_avg_sq && opt->step >= 1), B200RNN_EINVAL,
+               "comm_allreduce_update_nvls: Adam needs exp_avg/exp_avg_sq and step >= 1");
+  const OptScalars o = make_opt_scalars(opt);
+  int64_t shard = (n4 + ctx->world - 1) / ctx->world;
+  shard = (shard + 3) & ~int64_t(3);
+  int grid = num_sms();
+  const int64_t need = (n4 / kElems + kThreads - 1) / kThreads;
+  if (need < grid) grid = (int)(need < ctx->world ? ctx->world : need);   // small vectors: fewer CTAs, cheaper grid barrier
+  // the grid-barrier counter target depends on the grid: keep it fixed per region by always counting num_sms
+  grid = num_sms();
+  const unsigned int target = next_sync_call(ctx->base[ctx->rank]) * 2u * (unsigned)grid;
+  nvls_update_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(to_dev(ctx), (char*)mc_base, seq, target, rows, n_rows, n_params,
+                                                                  n_params + 2, params, params_heap_off, grad_heap_off, exp_avg,
+                                                                  exp_avg_sq, o, metrics, shard);
+  B200_CHECK_LAUNCH();
   return B200RNN_OK;
 }

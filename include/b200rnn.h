@@ -244,6 +244,16 @@ int b200rnn_symm_create(b200rnn_boot* b, int32_t device, int64_t bytes, b200rnn_
 int b200rnn_symm_pointers(b200rnn_symm* s, void** out /* [world]; out[rank] is the local region */);
 int b200rnn_symm_destroy(b200rnn_symm* s);
 
+/* Symmetric memory from the CUDA virtual-memory API (cuMemCreate, POSIX-fd exchange over Unix sockets)
+ * plus, when want_multicast != 0 and the node supports it, an NVSwitch multicast mapping of the same
+ * regions (csrc/runtime/symm_vmm.cpp).  ALLOCATES device memory; collective over the bootstrap; `tag`
+ * must be unique per node and job.  mc_out is NULL when multicast could not be set up. */
+typedef struct b200rnn_symm_vmm b200rnn_symm_vmm;
+int b200rnn_symm_vmm_create(b200rnn_boot* b, int32_t rank, int32_t world, int32_t device, int64_t bytes,
+                            int32_t tag, int32_t want_multicast, b200rnn_symm_vmm** out);
+int b200rnn_symm_vmm_pointers(b200rnn_symm_vmm* s, void** out /* [world] */, void** mc_out);
+int b200rnn_symm_vmm_destroy(b200rnn_symm_vmm* s);
+
 /* ---- N7 reducer: bucket assignment in reverse parameter order (c10d policy: 1 MiB first
  * bucket, then `cap`).  bucket_of[i] = bucket index of parameter i (bucket 0 holds the LAST
  * parameters, whose gradients are ready first). ---- */
@@ -267,7 +277,7 @@ typedef struct {
 /* Fills the off_* fields from world / max_blocks / inbox_floats / heap_bytes; returns region bytes. */
 int64_t b200rnn_comm_layout(b200rnn_comm_ctx* ctx);
 
-enum { B200RNN_ALGO_AUTO = 0, B200RNN_ALGO_ONESHOT = 1, B200RNN_ALGO_TWOSHOT = 2 };
+enum { B200RNN_ALGO_AUTO = 0, B200RNN_ALGO_ONESHOT = 1, B200RNN_ALGO_TWOSHOT = 2, B200RNN_ALGO_NVLS = 3 };
 
 /* K7: ONE kernel = fixed-order reduction of the n_rows local gradient rows + all-reduce over
  * NVLink peer memory (one-shot: every rank pushes its vector into every peer's inbox; two-shot:
@@ -281,6 +291,13 @@ int b200rnn_comm_allreduce_update(const b200rnn_comm_ctx* ctx, uint32_t seq, con
                                   int64_t params_heap_off, float* exp_avg, float* exp_avg_sq,
                                   const b200rnn_optim_desc* opt, float* metrics, int32_t algo,
                                   void* stream);
+/* NVLS form of K7: region from b200rnn_symm_vmm_create with multicast; the parameter arena
+ * (params_heap_off) and a gradient slot of the same padded size (grad_heap_off) live in the heap.
+ * The switch performs the reduction (multimem.ld_reduce) and the parameter broadcast (multimem.st). */
+int b200rnn_comm_allreduce_update_nvls(const b200rnn_comm_ctx* ctx, void* mc_base, uint32_t seq, const float* rows,
+                                       int32_t n_rows, int64_t n_params, float* params, int64_t params_heap_off,
+                                       int64_t grad_heap_off, float* exp_avg, float* exp_avg_sq,
+                                       const b200rnn_optim_desc* opt, float* metrics, void* stream);
 /* Plain in-place all-reduce (sum * scale) of buf[n] (n <= inbox_floats), same kernels without
  * the optimizer epilogue.  Shares the seq counter with b200rnn_comm_allreduce_update. */
 int b200rnn_comm_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, float* buf, int64_t n,

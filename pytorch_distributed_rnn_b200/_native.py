@@ -110,10 +110,14 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_symm_create": (i32, [vp, i32, i64, P(vp)]),
         "b200rnn_symm_pointers": (i32, [vp, P(vp)]),
         "b200rnn_symm_destroy": (i32, [vp]),
+        "b200rnn_symm_vmm_create": (i32, [vp, i32, i32, i32, i64, i32, i32, P(vp)]),
+        "b200rnn_symm_vmm_pointers": (i32, [vp, P(vp), P(vp)]),
+        "b200rnn_symm_vmm_destroy": (i32, [vp]),
         "b200rnn_bucket_plan": (i32, [P(i64), i32, i64, i64, P(i32), P(i32)]),
         # in-kernel collectives
         "b200rnn_comm_layout": (i64, [P(CommCtx)]),
         "b200rnn_comm_allreduce_update": (i32, [P(CommCtx), C.c_uint32, vp, i32, i64, vp, i64, vp, vp, P(OptimDesc), vp, i32, vp]),
+        "b200rnn_comm_allreduce_update_nvls": (i32, [P(CommCtx), vp, C.c_uint32, vp, i32, i64, vp, i64, i64, vp, vp, P(OptimDesc), vp, vp]),
         "b200rnn_comm_allreduce": (i32, [P(CommCtx), C.c_uint32, vp, i64, f32, vp]),
         "b200rnn_comm_broadcast": (i32, [P(CommCtx), C.c_uint32, i64, i64, i32, vp]),
         "b200rnn_comm_put": (i32, [P(CommCtx), C.c_uint32, i32, vp, i64, i64, vp]),

@@ -45,6 +45,7 @@ class _External:
 class SymmComm:
     kind = "symm"
     MAILBOX_BYTES = 1 << 16  # per source rank, for put/get
+    NVLS_MIN_BYTES = 1 << 20  # auto: in-switch reduction above this vector size (measured crossover)
 
     def __init__(self, info: Optional[RankInfo] = None, inbox_floats: Optional[int] = None,
                  heap_bytes: Optional[int] = None, max_blocks: int = 1 << 16, delay_ns: int = 0,
@@ -82,10 +83,37 @@ class SymmComm:
         region = self.lib.b200rnn_comm_layout(C.byref(ctx))
         if region <= 0:
             raise _native.NativeError("comm_layout failed")
+        # Region allocation: the VMM + NVSwitch-multicast form when the node supports NVLS (so that the
+        # in-switch reduction is available), else cudaMalloc + CUDA IPC.  B200RNN_SYMM=ipc|vmm overrides.
         self.symm = C.c_void_p()
-        _native.check(self.lib.b200rnn_symm_create(boot.handle, self.device.index, region, C.byref(self.symm)), "symm_create")
+        self.mc_base = None
+        self._vmm = False
         ptrs = (C.c_void_p * _native.MAX_PEERS)()
-        _native.check(self.lib.b200rnn_symm_pointers(self.symm, ptrs), "symm_pointers")
+        mode = os.environ.get("B200RNN_SYMM", "auto")
+        want_vmm = mode == "vmm" or (mode == "auto" and self.world > 1 and all(self.topology["multicast_supported"]))
+        if want_vmm:
+            mc = C.c_void_p()
+            rc = self.lib.b200rnn_symm_vmm_create(boot.handle, self.rank, self.world, self.device.index, region,
+                                                  int(boot.port) & 0x7FFFFFFF, 1, C.byref(self.symm))
+            ok = torch.tensor([1 if rc == 0 else 0], device=self.device)
+            if self.world > 1 and dist.is_initialized():
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN)     # all ranks take the same path
+            if int(ok.item()) == 1:
+                _native.check(self.lib.b200rnn_symm_vmm_pointers(self.symm, ptrs, C.byref(mc)), "symm_vmm_pointers")
+                self.mc_base = mc.value
+                self._vmm = True
+            else:
+                why = self.lib.b200rnn_last_error().decode("utf-8", "replace") if rc != 0 else "a peer failed"
+                if mode == "vmm":
+                    raise _native.NativeError(f"symm_vmm_create failed: {why}")
+                import logging
+                logging.warning("VMM/multicast symmetric memory unavailable (%s); using cudaMalloc + CUDA IPC", why)
+                if rc == 0:
+                    self.lib.b200rnn_symm_vmm_destroy(self.symm)
+                self.symm = C.c_void_p()
+        if not self._vmm:
+            _native.check(self.lib.b200rnn_symm_create(boot.handle, self.device.index, region, C.byref(self.symm)), "symm_create")
+            _native.check(self.lib.b200rnn_symm_pointers(self.symm, ptrs), "symm_pointers")
         for r in range(self.world):
             ctx.base[r] = ptrs[r]
         self.ctx = ctx
@@ -128,6 +156,9 @@ class SymmComm:
         flat, off = self.heap_tensor(n)
         arena = ParamArena(module, flat=flat)
         arena.heap_off = off
+        # gradient slot of the same (4-padded) size at a symmetric offset: operand of the in-switch reduction
+        n4 = (n + 3) // 4 * 4
+        arena.grad_heap_off = self.heap_alloc(n4 * 4)
         return arena
 
     # ---- collectives ----
@@ -138,6 +169,17 @@ class SymmComm:
         self._seq_ar += 1
         heap_off = getattr(arena, "heap_off", None)
         algo = self.algo if heap_off is not None else 1
+        nvls_ok = self.mc_base is not None and heap_off is not None and hasattr(arena, "grad_heap_off")
+        if algo == 3 and not nvls_ok:
+            raise RuntimeError("B200RNN_ALGO=3 (NVLS) needs a multicast-capable symmetric region")
+        if nvls_ok and (algo == 3 or (algo == 0 and arena.numel * 4 > self.NVLS_MIN_BYTES)):
+            _native.check(self.lib.b200rnn_comm_allreduce_update_nvls(
+                C.byref(self.ctx), self.mc_base, self._seq_ar, rows.data_ptr(), n_rows, arena.numel, arena.flat.data_ptr(),
+                heap_off, arena.grad_heap_off, opt.exp_avg.data_ptr(), opt.exp_avg_sq.data_ptr(), C.byref(optdesc),
+                metrics_slot.data_ptr(), self._sp()), "comm_allreduce_update_nvls")
+            return
+        if algo == 3:
+            algo = 0
         _native.check(self.lib.b200rnn_comm_allreduce_update(
             C.byref(self.ctx), self._seq_ar, rows.data_ptr(), n_rows, arena.numel, arena.flat.data_ptr(),
             heap_off if heap_off is not None else -1, opt.exp_avg.data_ptr(), opt.exp_avg_sq.data_ptr(),
@@ -234,6 +276,9 @@ class SymmComm:
             torch.cuda.synchronize(self.device)
             if self.world > 1:
                 self.boot.barrier()
-            self.lib.b200rnn_symm_destroy(self.symm)
+            if self._vmm:
+                self.lib.b200rnn_symm_vmm_destroy(self.symm)
+            else:
+                self.lib.b200rnn_symm_destroy(self.symm)
             self.symm = C.c_void_p()
         self.boot.close()

@@ -41,7 +41,9 @@ def main():
     res["allreduce_ok"] = ok
 
     # 2. fused all-reduce + Adam (one-shot and two-shot) vs torch Adam on the averaged gradient
-    for algo, name in ((1, "oneshot"), (2, "twoshot")):
+    res["nvls_available"] = comm.mc_base is not None
+    algos = [(1, "oneshot"), (2, "twoshot")] + ([(3, "nvls")] if comm.mc_base is not None else [])
+    for algo, name in algos:
         torch.manual_seed(5)
         lin = torch.nn.Linear(301, 97).to(dev)      # 29 294 parameters: several blocks, ragged tail
         ref = copy.deepcopy(lin)
