@@ -18,12 +18,12 @@ python -m pytorch_distributed_rnn_b200.parallel.launch -n $N -m pytorch_distribu
 for n in 1 2 4 8; do
   [ $n -le $N ] || continue
   run $n own_n$n --steps 200 --warmup 10
-  run $n ref_n$n --impl reference --steps 30 --warmup 3
+  if [ "${SKIP_REF:-0}" = 0 ] || [ $n = $N ]; then run $n ref_n$n --impl reference --steps 30 --warmup 3; fi
 done
 B200RNN_COMM=nccl run $N own_n${N}_ncclbaseline --steps 200 --warmup 10
 PORT=$((PORT+1))
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT bench/allreduce_sweep.py --delay-us 0,5,50 --out $OUT/allreduce_sweep_n$N.json > $OUT/allreduce_sweep_n$N.log 2>&1; echo "sweep n$N rc=$?"
-if [ $N -gt 2 ]; then
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $PORT bench/allreduce_sweep.py --delay-us 0,50 --out $OUT/allreduce_sweep_n$N.json > $OUT/allreduce_sweep_n$N.log 2>&1; echo "sweep n$N rc=$?"
+if [ $N -gt 2 ] && [ "${SKIP_N2_SWEEP:-0}" = 0 ]; then
 PORT=$((PORT+1))
 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port $PORT bench/allreduce_sweep.py --out $OUT/allreduce_sweep_n2.json > $OUT/allreduce_sweep_n2.log 2>&1; echo "sweep n2 rc=$?"
 fi
