@@ -522,7 +522,9 @@ static int launch_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, const flo
     // one-shot moves W*n floats per rank but pays a single NVLink latency; two-shot moves
     // 2(W-1)/W*n but pays two latencies and two grid barriers.  Crossover from the measured sweep
     // (bench/allreduce_sweep.py, profiles/).
-    algo = (n * 4 <= 512 * 1024 || ctx->world == 1 || heap_off < 0) ? B200RNN_ALGO_ONESHOT : B200RNN_ALGO_TWOSHOT;
+    // Measured (profiles/r1_allreduce_sweep_n{2,8}.md): one-shot wins while W * bytes <= ~128 KiB
+    // (W = 2: <= 64 KiB, W = 8: <= 16 KiB); above that its W-fold traffic and W flags per block lose.
+    algo = (n * 4 * ctx->world <= 128 * 1024 || ctx->world == 1 || heap_off < 0) ? B200RNN_ALGO_ONESHOT : B200RNN_ALGO_TWOSHOT;
   }
   if (algo == B200RNN_ALGO_ONESHOT) {
     B200_REQUIRE(one_blocks <= ctx->max_blocks, B200RNN_ETOOBIG, "comm one-shot: %lld blocks exceed max_blocks=%d",

@@ -82,9 +82,8 @@ def test_multirank_collectives_and_dp_invariance():
         assert cp.returncode == 0, f"rank {r}:\n{cp.stdout[-3000:]}\n{cp.stderr[-3000:]}"
         line = [l for l in cp.stdout.splitlines() if l.startswith("RESULT ")][-1]
         out = json.loads(line[7:])
-        for k, v in out.items():
-            if k.endswith("_ok"):
-                assert v is True, (r, out)
+        bad = {k: v for k, v in out.items() if k.endswith("_ok") and v is not True}
+        assert not bad, (r, bad, {k: v for k, v in out.items() if k.startswith("dp_param")})
 
 
 def test_bucket_plan_native_matches_python():
