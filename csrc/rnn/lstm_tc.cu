@@ -1,6 +1,6 @@
 // K2 (tensor-core form) — persistent LSTM forward for H = 32 on tcgen05 / TMEM.
 //
-// Same contract and stash layout as b200rnn_lstm_fwd (lstm_small.cu), different engine: the gate
+// Same contract and stash layout as b200rnn_lstm_fwd (lstm_small.inc), different engine: the gate
 // pre-activations of a whole batch tile are ONE small GEMM per timestep,
 //
 //        D[128 gate rows, 16 samples]  =  Wcat[128, K]  x  [x_t | h_{t-1}]^T[K, 16]
@@ -18,7 +18,7 @@
 // tf32 datapath reads) and D = a_hi*b_hi + a_lo*b_hi + a_hi*b_lo is accumulated in fp32 — the
 // "3xTF32" scheme; dropped terms are O(2^-20) relative, the same order as fp32 summation error.
 //
-// Replaces the FFMA gate GEMV of lstm_small.cu (FFMA issue bound: ~83 M warp-FFMAs per forward)
+// Replaces the FFMA gate GEMV of lstm_small.inc (FFMA issue bound: ~83 M warp-FFMAs per forward)
 // with ~18-24 MMA instructions per step.  Reference call site: src/motion/model.py:14.
 #include <stdlib.h>
 #include "../gemm/tc_common.cuh"

@@ -42,7 +42,7 @@ def _sources() -> list[Path]:
 
 
 def _headers_mtime() -> float:
-    hs = list(CSRC.rglob("*.cuh")) + list(CSRC.rglob("*.h")) + list(INCLUDE.rglob("*.h"))
+    hs = list(CSRC.rglob("*.cuh")) + list(CSRC.rglob("*.h")) + list(CSRC.rglob("*.inc")) + list(INCLUDE.rglob("*.h"))
     return max((h.stat().st_mtime for h in hs), default=0.0)
 
 

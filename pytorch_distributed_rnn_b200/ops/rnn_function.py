@@ -1,7 +1,7 @@
 """Autograd glue between torch modules and the fused recurrent kernels.
 
 ``fused_rnn(module, x)`` behaves like ``nn.LSTM.forward`` (returns ``out, (h_n, c_n)``)
-but runs ``b200rnn_lstm_fwd`` / ``b200rnn_lstm_bwd`` (csrc/rnn/lstm_small.cu) — the
+but runs ``b200rnn_lstm_fwd`` / ``b200rnn_lstm_bwd`` (csrc/rnn/lstm_small.inc) — the
 replacement for ATen ``lstm`` + its autograd backward that the reference reaches through
 ``self.lstm(x)`` / ``loss.backward()`` (src/motion/model.py:14, trainer/base.py:116).
 """
