@@ -61,6 +61,7 @@ def main():
     ap.add_argument("--max-bytes", type=int, default=256 << 20)
     ap.add_argument("--delay-us", type=str, default="0", help="comma list of injected delays (us)")
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--rows", type=int, default=1, help="local gradient rows to reduce inside the call (the fused step has ~90-144)")
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
     info = pg.init_distributed()
@@ -82,9 +83,9 @@ def main():
             lin = torch.nn.Linear(n - 1, 1, bias=True, device=dev) if n > 1 else None
             arena = comm.make_arena(lin)
             opt = FusedSGD(arena, lr=0.0)
-            rows = torch.ones(1, n + 2, device=dev)
+            rows = torch.ones(a.rows, n + 2, device=dev)
             slot = torch.zeros(2, device=dev)
-            row = {"bytes": nbytes, "world": world, "delay_us": delay}
+            row = {"bytes": nbytes, "world": world, "delay_us": delay, "rows": a.rows}
             for algo, name in ((1, "oneshot"), (2, "twoshot"), (3, "nvls")):
                 if algo == 3 and comm.mc_base is None:
                     continue
@@ -94,7 +95,7 @@ def main():
 
                 def fn():
                     opt.step_count += 1
-                    comm.allreduce_update(rows, 1, arena, opt, opt.desc(grad_scale=1.0 / world), slot)
+                    comm.allreduce_update(rows, a.rows, arena, opt, opt.desc(grad_scale=1.0 / world), slot)
                 row[f"{name}_us"] = timed(fn, a.iters, 5, dev)
             comm.algo = 0
             if delay == 0:

@@ -125,24 +125,25 @@ __device__ __forceinline__ F4 load4_cg(const float* src, long long i, long long 
 // Block b handles elements [b*1024, (b+1)*1024) (4 per thread, 128-bit peer stores); flags are per
 // (source, block), so blocks are independent and no grid-wide synchronisation exists.
 // ---------------------------------------------------------------------------
-template <bool UPDATE>
+template <bool UPDATE, int ELEMS>
 __global__ void __launch_bounds__(kThreads) oneshot_kernel(
     Ctx c, uint32_t seq, const float* __restrict__ rows, int n_rows, long long n, long long row_stride,
     float* buf /* UPDATE: params, else in/out vector */, float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
     OptScalars o, float scale, float* __restrict__ metrics) {
-  const long long i = ((long long)blockIdx.x * kThreads + threadIdx.x) * kElems;
+  const long long i = ((long long)blockIdx.x * kThreads + threadIdx.x) * ELEMS;
   F4 g;
   if (UPDATE) {
-    g = reduce_rows4(rows, n_rows, row_stride, i, n + 2);
+    g = reduce_rows4(rows, n_rows, row_stride, i, (ELEMS == 4 || i + 1 > n + 2) ? n + 2 : i + 1);
     if (metrics != nullptr) {
 #pragma unroll
-      for (int e = 0; e < 4; ++e) if (i + e >= n && i + e < n + 2) metrics[i + e - n] = g.v[e];   // stay local
+      for (int e = 0; e < ELEMS; ++e) if (i + e >= n && i + e < n + 2) metrics[i + e - n] = g.v[e];   // stay local
     }
   } else {
-    g = reduce_rows4(buf, 1, 0, i, n);
+    g = reduce_rows4(buf, 1, 0, i, (ELEMS == 4 || i + 1 > n) ? n : i + 1);
   }
   if (i < n) {
-    for (int p = 0; p < c.world; ++p) store4(inbox(c, p, seq, c.rank), g, i, n);   // peer stores (incl. self)
+    const long long lim = (ELEMS == 4 || i + 1 > n) ? n : i + 1;   // ELEMS == 1: only element i is mine
+    for (int p = 0; p < c.world; ++p) store4(inbox(c, p, seq, c.rank), g, i, lim);   // peer stores (incl. self)
   }
   __threadfence_system();
   __syncthreads();
@@ -155,12 +156,12 @@ __global__ void __launch_bounds__(kThreads) oneshot_kernel(
   if (i >= n) return;
   F4 sum; sum.v[0] = sum.v[1] = sum.v[2] = sum.v[3] = 0.0f;
   for (int s = 0; s < c.world; ++s) {   // fixed rank order => identical bits on every rank
-    const F4 t = load4_cg(inbox(c, c.rank, seq, s), i, n);
+    const F4 t = load4_cg(inbox(c, c.rank, seq, s), i, (ELEMS == 4 || i + 1 > n) ? n : i + 1);
 #pragma unroll
     for (int e = 0; e < 4; ++e) sum.v[e] += t.v[e];
   }
 #pragma unroll
-  for (int e = 0; e < 4; ++e) {
+  for (int e = 0; e < ELEMS; ++e) {
     const long long j = i + e;
     if (j >= n) break;
     if (UPDATE) {
@@ -517,7 +518,10 @@ static int launch_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, const flo
   OptScalars o{};
   if (update) o = make_opt_scalars(opt);
   const int64_t row_stride = n + 2;
-  const int64_t one_blocks = ((update ? n + 2 : n) + kBlockElems - 1) / kBlockElems;
+  // several gradient rows to reduce (the fused training step): 1 element per thread keeps 4x more
+  // threads on the row reduction; a single row: 4 elements per thread with 128-bit peer stores
+  const int one_elems = (update && n_rows > 1) ? 1 : kElems;
+  const int64_t one_blocks = ((update ? n + 2 : n) + kThreads * one_elems - 1) / (kThreads * one_elems);
   if (algo == B200RNN_ALGO_AUTO) {
     // one-shot moves W*n floats per rank but pays a single NVLink latency; two-shot moves
     // 2(W-1)/W*n but pays two latencies and two grid barriers.  Crossover from the measured sweep
@@ -531,8 +535,9 @@ static int launch_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, const flo
                  (long long)one_blocks, ctx->max_blocks);
     B200_REQUIRE(n <= ctx->inbox_floats, B200RNN_ETOOBIG, "comm one-shot: n=%lld exceeds inbox capacity %lld",
                  (long long)n, (long long)ctx->inbox_floats);
-    if (update) oneshot_kernel<true><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
-    else oneshot_kernel<false><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
+    if (update && one_elems == 1) oneshot_kernel<true, 1><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
+    else if (update) oneshot_kernel<true, 4><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
+    else oneshot_kernel<false, 4><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
   } else {
     int64_t shard = (n + ctx->world - 1) / ctx->world;
     shard = (shard + 3) & ~int64_t(3);                       // 16-byte aligned shard starts

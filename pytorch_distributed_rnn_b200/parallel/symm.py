@@ -170,6 +170,13 @@ class SymmComm:
         heap_off = getattr(arena, "heap_off", None)
         algo = self.algo if heap_off is not None else 1
         nvls_ok = self.mc_base is not None and heap_off is not None and hasattr(arena, "grad_heap_off")
+        if n_rows > 1 and heap_off is not None and self._picks_bulk(algo, arena.numel, nvls_ok):
+            # the bulk algorithms stream 4 elements per thread: reduce the per-CTA rows first with the
+            # 1-element-per-thread kernel (one extra launch) instead of serialising it inside them
+            _native.check(self.lib.b200rnn_reduce_rows(rows.data_ptr(), n_rows, arena.numel + 2, arena.grad.data_ptr(), 0,
+                                                       self._sp()), "reduce_rows")
+            _native.count_launch()
+            rows, n_rows = arena.grad, 1
         if algo == 3 and not nvls_ok:
             raise RuntimeError("B200RNN_ALGO=3 (NVLS) needs a multicast-capable symmetric region")
         if nvls_ok and (algo == 3 or (algo == 0 and arena.numel * 4 > self.NVLS_MIN_BYTES)):
@@ -184,6 +191,11 @@ class SymmComm:
             C.byref(self.ctx), self._seq_ar, rows.data_ptr(), n_rows, arena.numel, arena.flat.data_ptr(),
             heap_off if heap_off is not None else -1, opt.exp_avg.data_ptr(), opt.exp_avg_sq.data_ptr(),
             C.byref(optdesc), metrics_slot.data_ptr(), algo, self._sp()), "comm_allreduce_update")
+
+    def _picks_bulk(self, algo: int, n: int, nvls_ok: bool) -> bool:
+        if algo in (2, 3):
+            return True
+        return algo == 0 and self.world > 1 and n * 4 * self.world > 128 * 1024   # mirrors the native auto rule
 
     def allreduce_flat(self, t: torch.Tensor, average: bool = True) -> torch.Tensor:
         assert t.dtype == torch.float32 and t.is_contiguous()
@@ -200,6 +212,9 @@ class SymmComm:
     def broadcast_flat(self, t: torch.Tensor, root: int = 0) -> torch.Tensor:
         if self.world == 1:
             return t
+        # every rank must be done writing the destination (e.g. its own initial values) before the root's
+        # data may land there, and must have consumed it before the next broadcast: barrier on both sides
+        self.barrier()
         nbytes = t.numel() * t.element_size()
         off = self.heap_offset_of(t)
         staged = None

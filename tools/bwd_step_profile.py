@@ -1,6 +1,5 @@
 """clock64 breakdown of one backward step (layer 1, middle of the sequence, CTA 0)."""
 import ctypes as C, sys, torch
-sys.path.insert(0, '/root/repo')
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from pytorch_distributed_rnn_b200 import _native, MotionModel

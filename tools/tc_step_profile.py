@@ -1,5 +1,6 @@
 import ctypes as C, sys, torch
-sys.path.insert(0,'/root/repo')
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from pytorch_distributed_rnn_b200 import _native, MotionModel
 from pytorch_distributed_rnn_b200.ops.engine import FusedTrainEngine
 lib=_native.lib(); lib.b200rnn_tc_prof.argtypes=[C.c_void_p]; lib.b200rnn_tc_prof.restype=C.c_int
