@@ -75,6 +75,7 @@ class DistributedDataParallel(nn.Module):
             for i in b["ids"]:
                 self._bucket_of[i] = bi
         self._callback_queued = False
+        self._comm_stream = None
         self._slots = [self.arena.index[n] for n in names]
         for i, p in enumerate(self._params):
             if p.requires_grad:
@@ -126,8 +127,22 @@ class DistributedDataParallel(nn.Module):
         t = self.arena.grad[b["lo"]:b["hi"]]
         if isinstance(self.comm, TorchDistComm):
             b["work"] = dist.all_reduce(t, async_op=True)
+        elif t.is_cuda:
+            # in-kernel NVLink all-reduce on a side stream: it overlaps the rest of backward, which keeps
+            # running on the compute stream (one-shot kernels only wait on peers' pushes, never on a local
+            # grid barrier, so sharing the SMs with backward kernels cannot deadlock)
+            if self._comm_stream is None:
+                self._comm_stream = torch.cuda.Stream(t.device)
+            ready = torch.cuda.Event()
+            ready.record()
+            with torch.cuda.stream(self._comm_stream):
+                self._comm_stream.wait_event(ready)
+                self.comm.allreduce_flat(t, average=False)
+                done = torch.cuda.Event()
+                done.record()
+            b["work"] = done
         else:
-            self.comm.allreduce_flat(t, average=False)  # stream-ordered in-kernel all-reduce
+            self.comm.allreduce_flat(t, average=False)
             b["work"] = None
 
     def _finalize(self) -> None:
@@ -136,7 +151,10 @@ class DistributedDataParallel(nn.Module):
                 self._launch_bucket(b)
         for b in self.buckets:
             if b["work"] is not None:
-                b["work"].wait()
+                if isinstance(b["work"], torch.cuda.Event):
+                    torch.cuda.current_stream().wait_event(b["work"])
+                else:
+                    b["work"].wait()
                 b["work"] = None
             self.arena.grad[b["lo"]:b["hi"]].div_(self.comm.world)
             b["pending"] = len(b["ids"])
