@@ -120,6 +120,32 @@ def main():
     inv &= all(torch.equal(x, arena.flat[:arena.numel].clone()) for x in gather_all(arena.flat[:arena.numel].clone()))
     res["dp_invariance_ok"] = inv
 
+    # 4b. DDP wrapper on a multi-bucket autograd model: bucket all-reduces run on a side stream while
+    #     backward continues; gradients must equal the NCCL-averaged local gradients, identically on all ranks
+    from pytorch_distributed_rnn_b200.parallel.ddp import DistributedDataParallel as DDP
+    torch.manual_seed(11)
+    mlp = torch.nn.Sequential(torch.nn.Linear(512, 512), torch.nn.ReLU(), torch.nn.Linear(512, 512), torch.nn.ReLU(),
+                              torch.nn.Linear(512, 10)).to(dev)
+    twin = copy.deepcopy(mlp)
+    ddp = DDP(mlp, comm=comm, arena=comm.make_arena(mlp))
+    ov = len(ddp.buckets) >= 2
+    for it in range(3):
+        g = torch.Generator().manual_seed(1000 * it + rank)
+        xb = torch.randn(64, 512, generator=g).to(dev)
+        ddp.arena.zero_grad()
+        ddp(xb).square().mean().backward()
+        twin.zero_grad()
+        twin(xb).square().mean().backward()
+        torch.cuda.synchronize()
+        for p, q in zip(mlp.parameters(), twin.parameters()):
+            want = q.grad.clone()
+            dist.all_reduce(want)
+            want /= world
+            ov &= bool(torch.allclose(p.grad, want, rtol=1e-4, atol=1e-6))
+    ov &= all(torch.equal(x, ddp.arena.grad[:ddp.arena.numel].clone()) for x in gather_all(ddp.arena.grad[:ddp.arena.numel].clone()))
+    res["ddp_overlap_ok"] = ov
+    res["ddp_buckets"] = len(ddp.buckets)
+
     # 5. buffer-reuse soak with injected delay on one rank (straggler)
     comm.set_delay_ns(20000 if rank == world - 1 else 0)
     soak = True
