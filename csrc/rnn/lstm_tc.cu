@@ -308,7 +308,7 @@ using namespace b200rnn;
 extern "C" int b200rnn_lstm_fwd_tc(const b200rnn_model_desc* d, const float* params, const float* x, float* stash,
                                    int32_t training, void* stream) {
   B200_REQUIRE(d && params && x && stash, B200RNN_EINVAL, "lstm_fwd_tc: null argument");
-  B200_REQUIRE(b200rnn_rnn_small_supported(d), B200RNN_EUNSUPPORTED,
+  B200_REQUIRE(d->cell == B200RNN_CELL_LSTM && b200rnn_rnn_small_supported(d), B200RNN_EUNSUPPORTED,
                "lstm_fwd_tc: shape (cell=%d I=%d H=%d L=%d) not covered", d->cell, d->input_size, d->hidden_size, d->num_layers);
   TcFwdArgs a;
   a.x = x; a.params = params;

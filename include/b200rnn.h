@@ -113,6 +113,31 @@ int b200rnn_lstm_bwd(const b200rnn_model_desc* d, const float* params,
                      float loss_scale, const float* d_out, const float* d_hn,
                      const float* d_cn, float* scratch, void* stream);
 
+/* GRU members of the same fused family (hidden_size == 32, d->cell == B200RNN_CELL_GRU;
+ * torch gate order r, z, n; SURVEY P22 — the reference itself only builds nn.LSTM).  Same
+ * tiling, stash layout (h_seq | unused | per-step (r, z, n, W_hn h + b_hn)), scratch layout and
+ * fused head + cross-entropy as the LSTM entry points; a GRU has no cell state, so no d_cn. */
+int b200rnn_gru_fwd(const b200rnn_model_desc* d, const float* params,
+                    const float* x, float* stash, int32_t training, void* stream);
+int b200rnn_gru_bwd(const b200rnn_model_desc* d, const float* params,
+                    const float* x, const float* stash, const int64_t* labels,
+                    float loss_scale, const float* d_out, const float* d_hn,
+                    float* scratch, void* stream);
+
+/* Backward variants that additionally write the gradient of the network input: dx is
+ * [T][B][hidden_size] (time-major, the input zero-padded to hidden_size columns; columns
+ * >= input_size come out as zeros).  Same scratch and results as the plain entry points.
+ * (No counterpart in the reference, which never differentiates w.r.t. its input; needed for
+ * a drop-in recurrent layer that sits on top of other trainable layers.) */
+int b200rnn_lstm_bwd_dx(const b200rnn_model_desc* d, const float* params,
+                        const float* x, const float* stash, const int64_t* labels,
+                        float loss_scale, const float* d_out, const float* d_hn,
+                        const float* d_cn, float* scratch, float* dx, void* stream);
+int b200rnn_gru_bwd_dx(const b200rnn_model_desc* d, const float* params,
+                       const float* x, const float* stash, const int64_t* labels,
+                       float loss_scale, const float* d_out, const float* d_hn,
+                       float* scratch, float* dx, void* stream);
+
 /* Capacity of the scratch array compiled into the library for b200rnn_lstm_bwd_static. */
 #define B200RNN_STATIC_SCRATCH_FLOATS (4 * 1024 * 1024)
 

@@ -85,6 +85,10 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_lstm_fwd_tc": (i32, [P(ModelDesc), vp, vp, vp, i32, vp]),
         "b200rnn_tc_status": (i32, [P(i32)]),
         "b200rnn_lstm_bwd": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
+        "b200rnn_gru_fwd": (i32, [P(ModelDesc), vp, vp, vp, i32, vp]),
+        "b200rnn_gru_bwd": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp]),
+        "b200rnn_lstm_bwd_dx": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp]),
+        "b200rnn_gru_bwd_dx": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
         "b200rnn_lstm_bwd_static": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
         "b200rnn_reduce_rows": (i32, [vp, i32, i64, vp, i32, vp]),
         "b200rnn_head_fwd": (i32, [vp, i64, vp, vp, vp, i32, i32, i32, vp, vp, vp]),

@@ -44,8 +44,14 @@ class FusedTrainEngine:
         # recurrence is bound by the serial chain and a tcgen05.mma costs ~64 cycles to issue
         # whatever its N — see DESIGN.md), "tc" = tcgen05/TMEM recurrent kernel (3xTF32)
         self.fwd_kind = os.environ.get("B200RNN_FWD", "ffma")
-        self._fwd = self.lib.b200rnn_lstm_fwd_tc if self.fwd_kind == "tc" else self.lib.b200rnn_lstm_fwd
         self.model = model
+        lib = self.lib
+        if model.cell == "gru":   # GRU members of the fused family (no tcgen05 variant)
+            self._fwd = lib.b200rnn_gru_fwd
+            self._bwd = lambda d, p, x, st, y, scale, scratch, sp: lib.b200rnn_gru_bwd(d, p, x, st, y, scale, None, None, scratch, sp)
+        else:
+            self._fwd = lib.b200rnn_lstm_fwd_tc if self.fwd_kind == "tc" else lib.b200rnn_lstm_fwd
+            self._bwd = lambda d, p, x, st, y, scale, scratch, sp: lib.b200rnn_lstm_bwd(d, p, x, st, y, scale, None, None, None, scratch, sp)
         self.device = p0.device
         self.comm = comm
         self.arena = arena if arena is not None else (optimizer.arena if optimizer is not None else ParamArena(model))
@@ -106,8 +112,8 @@ class FusedTrainEngine:
         sp = _native.stream_ptr(self.device)
         a, opt = self.arena, self.optimizer
         _native.check(self._fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 1, sp), "lstm_fwd")
-        _native.check(self.lib.b200rnn_lstm_bwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(),
-                                                y.data_ptr(), 1.0 / B, None, None, None, buf["scratch"].data_ptr(), sp), "lstm_bwd")
+        _native.check(self._bwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(),
+                                                y.data_ptr(), 1.0 / B, buf["scratch"].data_ptr(), sp), "lstm_bwd")
         opt.step_count += 1
         slot = self.metrics[self.n_steps % self.METRIC_RING]
         o = opt.desc(grad_scale=1.0 / self.world)

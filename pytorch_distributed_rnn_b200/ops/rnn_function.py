@@ -1,7 +1,7 @@
 """Autograd glue between torch modules and the fused recurrent kernels.
 
 ``fused_rnn(module, x)`` behaves like ``nn.LSTM.forward`` (returns ``out, (h_n, c_n)``)
-but runs ``b200rnn_lstm_fwd`` / ``b200rnn_lstm_bwd`` (csrc/rnn/lstm_small.inc) — the
+but runs ``b200rnn_{lstm,gru}_fwd`` / ``b200rnn_{lstm,gru}_bwd`` (csrc/rnn/lstm_small.inc) — the
 replacement for ATen ``lstm`` + its autograd backward that the reference reaches through
 ``self.lstm(x)`` / ``loss.backward()`` (src/motion/model.py:14, trainer/base.py:116).
 """
@@ -71,29 +71,35 @@ def fused_supported(module, x: torch.Tensor) -> bool:
     return bool(lib.b200rnn_rnn_small_supported(C.byref(d)))
 
 
-class _FusedLSTMFn(torch.autograd.Function):
+class _FusedRNNFn(torch.autograd.Function):
+    """One persistent launch forward, one backward (+ fixed-order row reduction), LSTM or GRU."""
+
     @staticmethod
-    def forward(ctx, x: torch.Tensor, H: int, L: int, *weights: torch.Tensor):
+    def forward(ctx, x: torch.Tensor, cell: str, H: int, L: int, *weights: torch.Tensor):
         lib = _native.lib()
         B, T, I = x.shape
         x = x.contiguous()
-        d = canonical_desc("lstm", I, H, L, B, T, 0)
+        d = canonical_desc(cell, I, H, L, B, T, 0)
         params = packed_params(list(weights))
         stash = torch.empty(lib.b200rnn_rnn_stash_floats(C.byref(d)), dtype=torch.float32, device=x.device)
-        _native.check(lib.b200rnn_lstm_fwd(C.byref(d), params.data_ptr(), x.data_ptr(), stash.data_ptr(), 1,
-                                           _native.stream_ptr(x.device)), "lstm_fwd")
+        fwd = lib.b200rnn_lstm_fwd if cell == "lstm" else lib.b200rnn_gru_fwd
+        _native.check(fwd(C.byref(d), params.data_ptr(), x.data_ptr(), stash.data_ptr(), 1,
+                          _native.stream_ptr(x.device)), cell + "_fwd")
         _native.count_launch()
         n = L * T * B * H
         h_seq = stash[:n].view(L, T, B, H)
-        c_seq = stash[n:2 * n].view(L, T, B, H)
         ctx.save_for_backward(x, params, stash)
         ctx.desc = d
+        ctx.cell = cell
         ctx.shapes = [w.shape for w in weights]
         out = h_seq[L - 1].permute(1, 0, 2)  # [B,T,H] view of the time-major stash
-        return out, h_seq[:, T - 1], c_seq[:, T - 1]
+        if cell == "lstm":
+            c_seq = stash[n:2 * n].view(L, T, B, H)
+            return out, h_seq[:, T - 1], c_seq[:, T - 1]
+        return out, h_seq[:, T - 1]
 
     @staticmethod
-    def backward(ctx, d_out, d_hn, d_cn):
+    def backward(ctx, d_out, d_hn, d_cn=None):
         lib = _native.lib()
         x, params, stash = ctx.saved_tensors
         d = ctx.desc
@@ -105,9 +111,22 @@ class _FusedLSTMFn(torch.autograd.Function):
         d_hn = d_hn.contiguous() if d_hn is not None else None
         d_cn = d_cn.contiguous() if d_cn is not None else None
         sp = _native.stream_ptr(dev)
-        _native.check(lib.b200rnn_lstm_bwd(C.byref(d), params.data_ptr(), x.data_ptr(), stash.data_ptr(), None,
-                                           1.0, _native.ptr(d_out), _native.ptr(d_hn), _native.ptr(d_cn),
-                                           scratch.data_ptr(), sp), "lstm_bwd")
+        head = (C.byref(d), params.data_ptr(), x.data_ptr(), stash.data_ptr(), None, 1.0,
+                _native.ptr(d_out), _native.ptr(d_hn))
+        if ctx.cell == "lstm":
+            head = head + (_native.ptr(d_cn),)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            # the *_bwd_dx kernels also emit the input gradient, time-major and padded to H columns
+            B, T, I = x.shape
+            dx_pad = torch.empty(T, B, d.hidden_size, dtype=torch.float32, device=dev)
+            fn = lib.b200rnn_lstm_bwd_dx if ctx.cell == "lstm" else lib.b200rnn_gru_bwd_dx
+            rc = fn(*head, scratch.data_ptr(), dx_pad.data_ptr(), sp)
+            dx = dx_pad[:, :, :I].permute(1, 0, 2)
+        else:
+            fn = lib.b200rnn_lstm_bwd if ctx.cell == "lstm" else lib.b200rnn_gru_bwd
+            rc = fn(*head, scratch.data_ptr(), sp)
+        _native.check(rc, ctx.cell + "_bwd")
         row = d.n_params + 2
         grad = torch.empty(row, dtype=torch.float32, device=dev)
         _native.check(lib.b200rnn_reduce_rows(scratch.data_ptr(), nc.value, row, grad.data_ptr(), 0, sp), "reduce_rows")
@@ -119,15 +138,14 @@ class _FusedLSTMFn(torch.autograd.Function):
                 k *= s
             grads.append(grad[off:off + k].view(shp))
             off += k
-        # d/dx of the bottom layer is not produced by the fused kernels (the reference never uses it)
-        return (None, None, None, *grads)
+        return (dx, None, None, None, *grads)
 
 
 def fused_rnn(module, x: torch.Tensor):
-    if module.cell != "lstm":
-        raise NotImplementedError("fused GRU kernels are not available for this shape")
+    """``nn.LSTM`` / ``nn.GRU`` forward semantics on the fused small-hidden kernels."""
     xb = x if module.batch_first else x.transpose(0, 1)
-    out, h_n, c_n = _FusedLSTMFn.apply(xb, module.hidden_size, module.num_layers, *module.flat_weights())
-    if not module.batch_first:
-        out = out.transpose(0, 1)
-    return out, (h_n, c_n)
+    res = _FusedRNNFn.apply(xb, module.cell, module.hidden_size, module.num_layers, *module.flat_weights())
+    out = res[0] if module.batch_first else res[0].transpose(0, 1)
+    if module.cell == "lstm":
+        return out, (res[1], res[2])
+    return out, res[1]
