@@ -56,8 +56,21 @@ def main():
     for l in range(a.layers):
         i = a.input if l == 0 else a.hidden
         flops += 2 * 4 * a.hidden * (i + a.hidden) * a.seq * a.batch * 3   # fwd + 2x bwd
+    def fwd_ours():
+        with torch.no_grad():
+            ours(x)
+
+    def fwd_stock():
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            stock(x)
+
     t_ours, t_stock = timed(step_ours), timed(step_stock)
+    t_fwd_ours, t_fwd_stock = timed(fwd_ours), timed(fwd_stock)
+    from pytorch_distributed_rnn_b200.ops.gemm import gemm_status, persist_status
     print(json.dumps({"config": vars(a), "ours_ms": t_ours, "stock_cudnn_bf16_ms": t_stock,
+                      "ours_fwd_ms": t_fwd_ours, "stock_fwd_ms": t_fwd_stock,
+                      "persist_env": __import__("os").environ.get("B200RNN_PERSIST", "1"),
+                      "gemm_status": gemm_status(), "persist_status": persist_status(),
                       "ours_tflops": flops / t_ours / 1e9, "stock_tflops": flops / t_stock / 1e9,
                       "samples_per_s_ours": a.batch / t_ours * 1e3}))
 

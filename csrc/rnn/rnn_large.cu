@@ -8,10 +8,11 @@
 //                         dX = dG x W_ih; dW_ih = dG^T x X; dW_hh = dG^T x H_prev; db = colsum(dG)   (K4)
 //
 // bf16 operands, fp32 accumulation / cell state (BASELINE.json config 4: "2-layer LSTM hidden=1024,
-// seq_len=512, bf16").  The whole time loop is driven from this file (one C call per direction), so
-// the host cost per step is a kernel launch, not a Python round trip.  This is the per-timestep
-// ("standard algorithm") formulation; the weights are re-read from L2 each step — a persistent
-// kernel sharding W_hh across the SMs' shared memory is the planned replacement.
+// seq_len=512, bf16").  The whole time loop is driven from this file (one C call per direction).
+// Where the persistent kernels of rnn_persist.cu cover the shape (LSTM, H % 64 == 0, H / 8 <= #SMs,
+// B <= 128) the time loop of a layer is ONE cooperative launch with W_hh sharded across the SMs'
+// shared memory; otherwise it is the per-timestep formulation below (a GEMM + a cell kernel per step,
+// weights re-read from L2 each step).
 // Reference call sites: src/motion/model.py:9-17 (nn.LSTM fwd), trainer/base.py:116 (autograd bwd).
 #include <cuda_bf16.h>
 #include "../common.cuh"
@@ -19,6 +20,12 @@
 extern "C" int b200rnn_gemm_bf16(const void*, const void*, void*, const float*, int32_t, int32_t, int32_t, int32_t,
                                  int32_t, int32_t, int32_t, int32_t, void*);
 extern "C" int b200rnn_transpose_cast_bf16(const float*, void*, int32_t, int32_t, int64_t, int64_t, void*);
+// persistent time loops (rnn_persist.cu)
+extern "C" int b200rnn_rnn_persist_supported(const b200rnn_model_desc*);
+extern "C" int64_t b200rnn_rnn_persist_stream_bytes(int32_t);
+extern "C" int b200rnn_lstm_persist_fwd(int32_t, int32_t, int32_t, float*, const void*, float*, float*, void*, void*, void*);
+extern "C" int b200rnn_lstm_persist_bwd(int32_t, int32_t, int32_t, const float*, const float*, const float*, const float*,
+                                        const float*, const void*, float*, void*, void*, void*, void*);
 
 namespace b200rnn {
 namespace {
@@ -215,6 +222,8 @@ extern "C" int64_t b200rnn_rnn_large_scratch_bytes(const b200rnn_model_desc* d) 
   tot += al((int64_t)d->batch * H * 4) * 4;         // dh_rec, dc, dh_direct, bias tmp
   tot += al((int64_t)G * H * 4);                    // fused bias
   tot += al(TB * pad8(inmax) * 4);                  // dX fp32 (padded ld)
+  tot += 256;                                       // grid-barrier words of the persistent kernels
+  tot += al(b200rnn_rnn_persist_stream_bytes(H));   // their double-buffered operand tile image
   return tot;
 }
 
@@ -229,6 +238,8 @@ struct Scratch {
   bf16 *dGT_b, *xT_b;
   float* dxa[2];
   float *dh0, *dh1, *dc, *tmp, *bias, *dX;
+  void* sync;
+  void* stream_img;
 };
 Scratch carve(const b200rnn_model_desc* d, void* scratch) {
   const int H = d->hidden_size, G = d->cell == B200RNN_CELL_LSTM ? 4 : 3;
@@ -249,6 +260,8 @@ Scratch carve(const b200rnn_model_desc* d, void* scratch) {
   s.dh0 = c.take<float>(Bh * 4); s.dh1 = c.take<float>(Bh * 4); s.dc = c.take<float>(Bh * 4); s.tmp = c.take<float>(Bh * 4);
   s.bias = c.take<float>((int64_t)G * H * 4);
   s.dX = c.take<float>(TB * pad8(inmax) * 4);
+  s.sync = c.take<char>(256);
+  s.stream_img = c.take<char>(b200rnn_rnn_persist_stream_bytes(H));
   return s;
 }
 }  // namespace
@@ -284,6 +297,9 @@ extern "C" int b200rnn_rnn_large_fwd(const b200rnn_model_desc* d, const float* p
       B200_CHECK_CUDA(cudaMemcpyAsync(sc.bias, params + d->off_bih[l], (size_t)G * H * 4, cudaMemcpyDeviceToDevice, s));
       add_inplace<<<grid_for((int64_t)G * H), 256, 0, s>>>(sc.bias, params + d->off_bhh[l], (int64_t)G * H);
       RC(b200rnn_gemm_bf16(xb, sc.wih_b, gates, sc.bias, (int32_t)TB, G * H, inp8, inp8, inp8, G * H, 0, 0, stream));
+      if (b200rnn_rnn_persist_supported(d)) {
+        RC(b200rnn_lstm_persist_fwd(T, B, H, gates, sc.whh_b, c, h, sc.stream_img, sc.sync, stream));
+      } else
       for (int t = 0; t < T; ++t) {
         float* gt = gates + t * Bh * G;
         if (t > 0) RC(b200rnn_gemm_bf16(hb + (t - 1) * Bh, sc.whh_b, gt, nullptr, B, G * H, H, H, H, G * H, 1, 0, stream));
@@ -350,6 +366,10 @@ extern "C" int b200rnn_rnn_large_bwd(const b200rnn_model_desc* d, const float* p
     }
     float* dh_cur = sc.dh0;
     float* dh_nxt = sc.dh1;
+    if (lstm && b200rnn_rnn_persist_supported(d)) {
+      RC(b200rnn_lstm_persist_bwd(T, B, H, gates, c, dh_ext, d_hn ? d_hn + l * Bh : nullptr, d_cn ? d_cn + l * Bh : nullptr,
+                                  sc.whhT_b, sc.dG, sc.dG_b, sc.stream_img, sc.sync, stream));
+    } else
     for (int t = T - 1; t >= 0; --t) {
       const float* dhe = dh_ext ? dh_ext + t * Bh : nullptr;
       if (lstm) {

@@ -229,6 +229,22 @@ int b200rnn_rnn_large_bwd(const b200rnn_model_desc* d, const float* params, cons
                           const void* stash, void* scratch, const float* d_out_tm, const float* d_hn,
                           const float* d_cn, float* grad_out, float* dx_tm, void* stream);
 
+/* Persistent time loops of the large-hidden LSTM (csrc/rnn/rnn_persist.cu): one cooperative launch
+ * per layer and direction, W_hh sharded across the SMs' shared memory, h_t / dG_t exchanged through
+ * L2 with a grid barrier per step.  b200rnn_rnn_large_fwd/bwd use them automatically when
+ * b200rnn_rnn_persist_supported(d) (LSTM, hidden % 64 == 0, hidden / 8 <= #SMs, batch <= 128;
+ * B200RNN_PERSIST=0 disables).  `sync` is 256 bytes of device memory, zeroed by the call.
+ * b200rnn_persist_status() returns non-zero after a bounded wait inside the kernels timed out. */
+int b200rnn_rnn_persist_supported(const b200rnn_model_desc* d);
+int64_t b200rnn_rnn_persist_stream_bytes(int32_t H);   /* size of `stream_img` below */
+int b200rnn_lstm_persist_fwd(int32_t T, int32_t B, int32_t H, float* gates, const void* whh_bf16,
+                             float* c, float* h, void* stream_img, void* sync, void* stream);
+int b200rnn_lstm_persist_bwd(int32_t T, int32_t B, int32_t H, const float* gates, const float* c,
+                             const float* dh_ext, const float* d_hn, const float* d_cn,
+                             const void* whhT_bf16, float* dG, void* dG_bf16, void* stream_img, void* sync,
+                             void* stream);
+int b200rnn_persist_status(int32_t* status);
+
 /* ---- L2 flush helper for benchmarking (writes `bytes` of scratch). */
 int b200rnn_l2_flush(void* scratch, int64_t bytes, void* stream);
 

@@ -87,6 +87,8 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_lstm_bwd": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
         "b200rnn_gru_fwd": (i32, [P(ModelDesc), vp, vp, vp, i32, vp]),
         "b200rnn_gru_bwd": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp]),
+        "b200rnn_rnn_persist_supported": (i32, [P(ModelDesc)]),
+        "b200rnn_persist_status": (i32, [P(i32)]),
         "b200rnn_lstm_bwd_dx": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp]),
         "b200rnn_gru_bwd_dx": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
         "b200rnn_lstm_bwd_static": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),

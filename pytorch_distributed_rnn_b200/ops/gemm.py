@@ -55,3 +55,11 @@ def gemm_status() -> int:
     st = C.c_int32(0)
     _native.check(_native.lib().b200rnn_gemm_status(C.byref(st)), "gemm_status")
     return st.value
+
+
+def persist_status() -> int:
+    """Non-zero once a bounded wait inside the persistent recurrent kernels (csrc/rnn/rnn_persist.cu) timed out."""
+    import ctypes as C
+    st = C.c_int32(0)
+    _native.check(_native.lib().b200rnn_persist_status(C.byref(st)), "persist_status")
+    return st.value

@@ -4,7 +4,7 @@ import torch
 from torch import nn
 
 from pytorch_distributed_rnn_b200 import FusedGRU, FusedLSTM
-from pytorch_distributed_rnn_b200.ops.gemm import gemm_status
+from pytorch_distributed_rnn_b200.ops.gemm import gemm_status, persist_status
 
 pytestmark = pytest.mark.gpu
 
@@ -17,6 +17,9 @@ def _rel(a, b):
     (FusedLSTM, nn.LSTM, 9, 64, 2, 24, 12),
     (FusedLSTM, nn.LSTM, 40, 128, 1, 16, 20),
     (FusedLSTM, nn.LSTM, 64, 256, 2, 8, 6),
+    (FusedLSTM, nn.LSTM, 24, 128, 2, 80, 9),    # 64 < B <= 128: the M = 128 persistent variants
+    (FusedLSTM, nn.LSTM, 16, 1024, 1, 64, 5),   # the scaled configuration's geometry (128 CTAs, 64 KB W shards)
+    (FusedLSTM, nn.LSTM, 16, 192, 1, 130, 4),   # B > 128: per-timestep formulation
     (FusedGRU, nn.GRU, 9, 64, 2, 24, 12),
     (FusedGRU, nn.GRU, 9, 40, 2, 16, 10),      # H % 8 == 0 but outside the fused small-hidden family
     (FusedGRU, nn.GRU, 48, 128, 1, 8, 7),
@@ -38,6 +41,7 @@ def test_large_path_forward_backward(cls, stock, I, H, L, B, T):
     ((ro * wo).sum() + rh.sum()).backward()
     torch.cuda.synchronize()
     assert gemm_status() == 0
+    assert persist_status() == 0
     assert _rel(out.detach().cpu(), ro.detach()) < 3e-2
     assert _rel(h.detach().cpu(), rh.detach()) < 3e-2
     if isinstance(st, tuple):
