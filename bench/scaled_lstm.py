@@ -67,10 +67,14 @@ def main():
     t_ours, t_stock = timed(step_ours), timed(step_stock)
     t_fwd_ours, t_fwd_stock = timed(fwd_ours), timed(fwd_stock)
     from pytorch_distributed_rnn_b200.ops.gemm import gemm_status, persist_status
+    with torch.no_grad():   # sanity: same weights, so the two outputs agree to bf16 rounding
+        o1 = ours(x)[0].float()
+        o2 = stock(x)[0].float()
+        out_rel_err = float((o1 - o2).abs().max() / (o2.abs().max() + 1e-6))
     print(json.dumps({"config": vars(a), "ours_ms": t_ours, "stock_cudnn_bf16_ms": t_stock,
                       "ours_fwd_ms": t_fwd_ours, "stock_fwd_ms": t_fwd_stock,
                       "persist_env": __import__("os").environ.get("B200RNN_PERSIST", "1"),
-                      "gemm_status": gemm_status(), "persist_status": persist_status(),
+                      "gemm_status": gemm_status(), "persist_status": persist_status(), "out_rel_err_vs_fp32": out_rel_err,
                       "ours_tflops": flops / t_ours / 1e9, "stock_tflops": flops / t_stock / 1e9,
                       "samples_per_s_ours": a.batch / t_ours * 1e3}))
 
