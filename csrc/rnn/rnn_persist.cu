@@ -67,6 +67,27 @@ __device__ __forceinline__ void red_release_gpu(unsigned* p, unsigned v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+// ---- thread-block-cluster helpers (2-D backward: partial sums exchanged through distributed shared memory) ----
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_v4(uint32_t addr, float x, float y, float z, float w) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_remote_release(uint32_t addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(addr) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_acq_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 // Bounded waits that also drain quickly once anybody has aborted.
@@ -75,6 +96,20 @@ __device__ __forceinline__ bool wait_mbar(uint64_t* bar, uint32_t parity, volati
   const long long t0 = clock64();
   for (;;) {
     if (mbar_try_wait(bar, parity)) return true;
+    if (*s_abort) return false;
+    if (clock64() - t0 > kSpinBudget) {
+      *s_abort = 1;
+      atomicExch(&sync->abort, 1u);
+      atomicCAS(&g_persist_error, 0, code);
+      return false;
+    }
+  }
+}
+__device__ __forceinline__ bool wait_mbar_cluster(uint64_t* bar, uint32_t parity, volatile int* s_abort, PersistSync* sync, int code) {
+  if (mbar_try_wait_acq_cluster(bar, parity)) return true;
+  const long long t0 = clock64();
+  for (;;) {
+    if (mbar_try_wait_acq_cluster(bar, parity)) return true;
     if (*s_abort) return false;
     if (clock64() - t0 > kSpinBudget) {
       *s_abort = 1;
@@ -120,10 +155,18 @@ struct PersistArgs {
   int B, H, T, stages;
 };
 
-template <int BM, bool BWD> struct PersistCfg {
-  // MMA N: fwd 4 gates x 8 units; bwd 8 units (M = 128 needs N % 16 == 0: the 8 rows are loaded twice
-  // and accumulator columns 8-15 are ignored)
-  static constexpr int N = BWD ? (BM == 128 ? 2 * UC : UC) : 4 * UC;
+// MODE 0: forward.  MODE 1: backward, CTA = 8 output units x all K = 4H (every CTA streams the whole dG).
+// MODE 2: backward, 2-D: a cluster of 4 CTAs owns 32 output units; CTA `ks` of the cluster multiplies the
+//         K quarter [ks*H, (ks+1)*H) (= gate ks of dG) into partial sums for all 32 units, the four partials
+//         are exchanged through distributed shared memory, and each CTA finishes 8 of the units.  Every CTA
+//         then streams a quarter of dG (what the forward streams of h) instead of all of it.
+template <int BM, int MODE> struct PersistCfg {
+  static constexpr bool BWD = MODE != 0;
+  static constexpr bool TWOD = MODE == 2;
+  // MMA N: fwd 4 gates x 8 units; 2-D bwd 32 units; 1-D bwd 8 units (M = 128 needs N % 16 == 0: the 8 rows
+  // are loaded twice and accumulator columns 8-15 are ignored)
+  static constexpr int N = MODE == 1 ? (BM == 128 ? 2 * UC : UC) : 4 * UC;
+  static constexpr int XBUF = TWOD ? 4 * BM * UC * 4 : 0;   // bytes: [4 source CTAs][BM rows][8 units] fp32
   static constexpr int W_CHUNK = N * PK * 2;          // bytes of the resident weight shard per K chunk
   static constexpr int A_TILE = BM * PK * 2;          // bytes of the streamed operand per K chunk
   // one accumulator per MMA-issuing warp (TMEM columns [i*ACC_STRIDE, +N)); the epilogue adds them up
@@ -138,25 +181,31 @@ constexpr int NISS = 4;           // MMA-issuing warps: 1, 9, 10, 11 (one per K-
 constexpr int NTHREADS = 384;     // warps 4-7: epilogue (TMEM lane quarters 0-3)
 static_assert(NISS == PK / 16, "issuer i owns K-step i of every chunk");
 
-template <int BM, bool BWD>
+template <int BM, int MODE>
 __global__ void __launch_bounds__(NTHREADS, 1)
 lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs a) {
-  using Cfg = PersistCfg<BM, BWD>;
+  using Cfg = PersistCfg<BM, MODE>;
   constexpr int N = Cfg::N;
+  constexpr bool BWD = Cfg::BWD, TWOD = Cfg::TWOD;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int H = a.H, B = a.B, T = a.T;
-  const int KTOT = BWD ? 4 * H : H;
+  const int KTOT = MODE == 1 ? 4 * H : H;              // K extent of this CTA's product
   const int nk = KTOT / PK;
+  const int nk_img = (BWD ? 4 * H : H) / PK;           // chunks of the streamed operand's tile image
+  const int ks = TWOD ? (int)(blockIdx.x & 3u) : 0;    // 2-D: rank in the cluster = K quarter
+  const int ngi = (int)(blockIdx.x >> 2);              // 2-D: group of 32 output units
   const int ng = (nk + Cfg::CG - 1) / Cfg::CG;         // chunk groups per step
   uint8_t* sW = smem;                                  // [nk][N rows][128 B] swizzled atoms
   uint8_t* sA = sW + (size_t)nk * Cfg::W_CHUNK;        // ring of [CG][BM rows][128 B] stages
   const int PSTAGES = a.stages;
-  uint64_t* full = reinterpret_cast<uint64_t*>(sA + PSTAGES * Cfg::STAGE);
+  float* xbuf = reinterpret_cast<float*>(sA + PSTAGES * Cfg::STAGE);   // 2-D: partials received from the cluster
+  uint64_t* full = reinterpret_cast<uint64_t*>(sA + PSTAGES * Cfg::STAGE + Cfg::XBUF);
   uint64_t* empty = full + PSTAGES;
   uint64_t* tmem_full = empty + PSTAGES;
   uint64_t* wbar = tmem_full + 1;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wbar + 1);
+  uint64_t* xbar = wbar + 1;                           // 2-D: one arrival per peer CTA and step
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(xbar + 1);
   volatile int* s_abort = reinterpret_cast<volatile int*>(tmem_slot + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -172,6 +221,7 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
     for (int i = 0; i < PSTAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], NISS); }
     mbar_init(tmem_full, NISS);
     mbar_init(wbar, 1);
+    mbar_init(xbar, 3);
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<Cfg::TM_COLS>(tmem_slot);
@@ -192,7 +242,11 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
       // resident weight shard, once
       mbar_expect_tx(wbar, (uint32_t)(nk * Cfg::W_CHUNK));
       for (int kb = 0; kb < nk; ++kb) {
-        if (BWD) {
+        if (TWOD) {
+#pragma unroll
+          for (int r = 0; r < 4; ++r)                                   // W_hh^T rows = my group's 32 units, my K quarter
+            tma_load_2d(sW + (size_t)kb * Cfg::W_CHUNK + r * (UC * PK * 2), &tma_w, wbar, ks * H + kb * PK, ngi * 32 + r * UC);
+        } else if (BWD) {
 #pragma unroll
           for (int r = 0; r < N / UC; ++r)                                                  // W_hh^T rows = my units
             tma_load_2d(sW + (size_t)kb * Cfg::W_CHUNK + r * (UC * PK * 2), &tma_w, wbar, kb * PK, u0);
@@ -206,7 +260,8 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
     int it = 0;
     for (int s_i = 1; s_i < T; ++s_i) {
       // step s_i consumes what step s_i - 1 wrote (forward: h_{t-1}; backward: dG_{t+1}) into buffer (s_i-1)&1
-      const uint8_t* src = reinterpret_cast<const uint8_t*>(a.stream) + (size_t)((s_i - 1) & 1) * nk * Cfg::A_TILE;
+      const uint8_t* src = reinterpret_cast<const uint8_t*>(a.stream) +
+                           ((size_t)((s_i - 1) & 1) * nk_img + (size_t)ks * nk) * Cfg::A_TILE;
       const bool stamp = blockIdx.x == 0 && s_i == T / 2 && pidx == 0;
       PSTAMP(0);
       const bool go = wait_grid(a.sync, (unsigned)s_i * ncta, s_abort, 10);
@@ -343,6 +398,44 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
           }
         }
       }
+      // ---- 2-D backward: acc holds my K quarter's partial sums for the cluster's 32 units.  Send the 8-unit
+      // slices the peers finish into their xbuf[my rank], keep mine, and add what the peers sent me. ----
+      float dhrec[UC];
+#pragma unroll
+      for (int i = 0; i < UC; ++i) dhrec[i] = BWD ? acc[i % N] : 0.0f;
+      if (TWOD && s_i > 0) {
+        const uint32_t xb_local = smem_u32(xbuf + ((size_t)ks * BM + row) * UC);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          if (p == ks) {
+#pragma unroll
+            for (int i = 0; i < UC; ++i) dhrec[i] = acc[(p * UC + i) % N];
+          } else if (live) {
+            const uint32_t ra = map_to_cta(xb_local, (uint32_t)p);
+            st_cluster_v4(ra, acc[(p * UC + 0) % N], acc[(p * UC + 1) % N], acc[(p * UC + 2) % N], acc[(p * UC + 3) % N]);
+            st_cluster_v4(ra + 16, acc[(p * UC + 4) % N], acc[(p * UC + 5) % N], acc[(p * UC + 6) % N], acc[(p * UC + 7) % N]);
+          }
+        }
+        epi_bar_sync();   // the CTA's slices are stored; one release-arrive per peer covers them all
+        if (threadIdx.x == 128) {
+          const uint32_t xbar_local = smem_u32(xbar);
+#pragma unroll
+          for (int p = 0; p < 4; ++p)
+            if (p != ks) mbar_arrive_remote_release(map_to_cta(xbar_local, (uint32_t)p));
+        }
+        const bool okx = __all_sync(0xffffffffu, wait_mbar_cluster(xbar, (uint32_t)(s_i - 1) & 1, s_abort, a.sync, 31));
+        if (okx && live) {
+#pragma unroll
+          for (int p = 0; p < 4; ++p) {
+            if (p != ks) {
+              const float4* xp = reinterpret_cast<const float4*>(xbuf + ((size_t)p * BM + row) * UC);
+              const float4 x0 = xp[0], x1 = xp[1];
+              dhrec[0] += x0.x; dhrec[1] += x0.y; dhrec[2] += x0.z; dhrec[3] += x0.w;
+              dhrec[4] += x1.x; dhrec[5] += x1.y; dhrec[6] += x1.z; dhrec[7] += x1.w;
+            }
+          }
+        }
+      }
       tc_fence_before_sync();   // my TMEM reads are done before the arrive lets the next step's MMAs overwrite D
       const float gin[4][UC] = {
           {gv[0][0].x, gv[0][0].y, gv[0][0].z, gv[0][0].w, gv[0][1].x, gv[0][1].y, gv[0][1].z, gv[0][1].w},
@@ -369,7 +462,7 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
           uint4 pk;
           pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
           pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
-          *reinterpret_cast<uint4*>(stream_unit(a.stream, s_i & 1, nk, BM, row, u0)) = pk;
+          *reinterpret_cast<uint4*>(stream_unit(a.stream, s_i & 1, nk_img, BM, row, u0)) = pk;
         }
         PSTAMP(18);
         epi_bar_sync();
@@ -403,7 +496,7 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
 #pragma unroll
           for (int i = 0; i < UC; ++i) {
             const float ig = gin[0][i], fg = gin[1][i], gg = gin[2][i], og = gin[3][i];
-            const float dh = dhe[i] + acc[i % N];
+            const float dh = dhe[i] + dhrec[i];
             const float tc = tanh_f(cvv[i]);
             const float dct = fmaf(dh * og, 1.0f - tc * tc, carry[i]);
             dg[0][i] = dct * gg * ig * (1.0f - ig);
@@ -419,7 +512,7 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
             uint4 pk;
             pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
             pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
-            *reinterpret_cast<uint4*>(stream_unit(a.stream, s_i & 1, nk, BM, row, g * H + u0)) = pk;
+            *reinterpret_cast<uint4*>(stream_unit(a.stream, s_i & 1, nk_img, BM, row, g * H + u0)) = pk;
             dgp[g] = pk;
           }
         }
@@ -477,40 +570,65 @@ constexpr size_t kSmemFixed = 2 * MAX_STAGES * 8 + 64 + 1024;   // barriers + sl
 constexpr int kMinStages = 2;
 
 // ring depth: the whole streamed operand of a step if it fits next to the weight shard, else what does
-template <int BM, bool BWD>
+template <int BM, int MODE>
 int persist_stages(int H) {
-  using Cfg = PersistCfg<BM, BWD>;
-  const int nk = (BWD ? 4 * H : H) / PK;
+  using Cfg = PersistCfg<BM, MODE>;
+  const int nk = (MODE == 1 ? 4 * H : H) / PK;
   const int ng = (nk + Cfg::CG - 1) / Cfg::CG;
-  const size_t w = (size_t)nk * Cfg::W_CHUNK;
+  const size_t w = (size_t)nk * Cfg::W_CHUNK + Cfg::XBUF;
   if (w + kSmemFixed + (size_t)kMinStages * Cfg::STAGE > kSmemLimit) return 0;
   int st = (int)((kSmemLimit - w - kSmemFixed) / Cfg::STAGE);
   if (st > ng && ng >= kMinStages) st = ng;
   if (st > MAX_STAGES) st = MAX_STAGES;
   return st;
 }
-template <int BM, bool BWD>
+template <int BM, int MODE>
 size_t persist_smem(int H) {
-  using Cfg = PersistCfg<BM, BWD>;
-  const int nk = (BWD ? 4 * H : H) / PK;
-  return (size_t)nk * Cfg::W_CHUNK + (size_t)persist_stages<BM, BWD>(H) * Cfg::STAGE + kSmemFixed;
+  using Cfg = PersistCfg<BM, MODE>;
+  const int nk = (MODE == 1 ? 4 * H : H) / PK;
+  return (size_t)nk * Cfg::W_CHUNK + (size_t)persist_stages<BM, MODE>(H) * Cfg::STAGE + Cfg::XBUF + kSmemFixed;
 }
 
-template <int BM, bool BWD>
+// Returns B200RNN_EUNSUPPORTED (without launching) when the grid cannot be made co-resident, so that the
+// caller can fall back to another decomposition.
+template <int BM, int MODE>
 int launch_persist(const CUtensorMap& mw, PersistArgs a, cudaStream_t s) {
-  a.stages = persist_stages<BM, BWD>(a.H);
+  a.stages = persist_stages<BM, MODE>(a.H);
   B200_REQUIRE(a.stages >= kMinStages, B200RNN_EUNSUPPORTED, "rnn_persist: weight shard of H=%d leaves no room for the operand ring", a.H);
-  const size_t smem = persist_smem<BM, BWD>(a.H);
-  auto kern = lstm_persist_kernel<BM, BWD>;
+  const size_t smem = persist_smem<BM, MODE>(a.H);
+  auto kern = lstm_persist_kernel<BM, MODE>;
   B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 0;
-  B200_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NTHREADS, smem));
   const int grid = a.H / UC;
-  B200_REQUIRE(per_sm * num_sms() >= grid, B200RNN_EUNSUPPORTED,
-               "rnn_persist: %d CTAs cannot be co-resident (%d per SM x %d SMs)", grid, per_sm, num_sms());
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid); cfg.blockDim = dim3(NTHREADS); cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  if (MODE == 2) {
+    // clusters of 4 CTAs (the K quarters of one 32-unit group), all clusters co-resident
+    at[1].id = cudaLaunchAttributeClusterDimension;
+    at[1].val.clusterDim.x = 4; at[1].val.clusterDim.y = 1; at[1].val.clusterDim.z = 1;
+    cfg.numAttrs = 2;
+    int n_clusters = 0;
+    const cudaError_t e = cudaOccupancyMaxActiveClusters(&n_clusters, (void*)kern, &cfg);
+    if (e != cudaSuccess) { cudaGetLastError(); n_clusters = 0; }
+    B200_REQUIRE(n_clusters * 4 >= grid, B200RNN_EUNSUPPORTED,
+                 "rnn_persist: %d clusters of 4 CTAs cannot be co-resident (%d fit)", grid / 4, n_clusters);
+  } else {
+    int per_sm = 0;
+    B200_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, NTHREADS, smem));
+    B200_REQUIRE(per_sm * num_sms() >= grid, B200RNN_EUNSUPPORTED,
+                 "rnn_persist: %d CTAs cannot be co-resident (%d per SM x %d SMs)", grid, per_sm, num_sms());
+  }
   B200_CHECK_CUDA(cudaMemsetAsync(a.sync, 0, sizeof(PersistSync), s));
   void* args[2] = {(void*)&mw, (void*)&a};
-  B200_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3(NTHREADS), args, smem, s));
+  const cudaError_t le = cudaLaunchKernelExC(&cfg, (void*)kern, args);
+  if (le != cudaSuccess && MODE == 2) {   // e.g. a driver that refuses cooperative + cluster launches
+    cudaGetLastError();
+    set_error("rnn_persist: clustered cooperative launch refused (%s)", cudaGetErrorString(le));
+    return B200RNN_EUNSUPPORTED;
+  }
+  B200_CHECK_CUDA(le);
   return B200RNN_OK;
 }
 
@@ -528,8 +646,8 @@ extern "C" int b200rnn_rnn_persist_supported(const b200rnn_model_desc* d) {
   const int H = d->hidden_size, B = d->batch;
   if (H % 64 != 0 || H < 64 || B < 1 || B > 128 || d->seq_len < 1) return 0;
   if (H / UC > num_sms()) return 0;
-  const int st = B <= 64 ? (persist_stages<64, true>(H) < persist_stages<64, false>(H) ? persist_stages<64, true>(H) : persist_stages<64, false>(H))
-                         : (persist_stages<128, true>(H) < persist_stages<128, false>(H) ? persist_stages<128, true>(H) : persist_stages<128, false>(H));
+  const int st = B <= 64 ? (persist_stages<64, 1>(H) < persist_stages<64, 0>(H) ? persist_stages<64, 1>(H) : persist_stages<64, 0>(H))
+                         : (persist_stages<128, 1>(H) < persist_stages<128, 0>(H) ? persist_stages<128, 1>(H) : persist_stages<128, 0>(H));
   return st >= kMinStages ? 1 : 0;
 }
 
@@ -549,8 +667,8 @@ extern "C" int b200rnn_lstm_persist_fwd(int32_t T, int32_t B, int32_t H, float* 
   PersistArgs a{};
   a.gates = gates; a.c = c; a.h = h; a.stream = (bf16*)stream_buf; a.sync = (PersistSync*)sync;
   a.B = B; a.H = H; a.T = T;
-  return bm == 64 ? launch_persist<64, false>(mw, a, (cudaStream_t)stream)
-                  : launch_persist<128, false>(mw, a, (cudaStream_t)stream);
+  return bm == 64 ? launch_persist<64, 0>(mw, a, (cudaStream_t)stream)
+                  : launch_persist<128, 0>(mw, a, (cudaStream_t)stream);
 }
 
 // Backward time loop of one layer.  gates / c: the forward stash; dh_ext: [T,B,H] gradient from above
@@ -570,8 +688,15 @@ extern "C" int b200rnn_lstm_persist_bwd(int32_t T, int32_t B, int32_t H, const f
   a.dh_ext = dh_ext; a.d_hn = d_hn; a.d_cn = d_cn; a.dG = dG; a.dG_b = (bf16*)dG_b;
   a.stream = (bf16*)stream_buf; a.sync = (PersistSync*)sync;
   a.B = B; a.H = H; a.T = T;
-  return bm == 64 ? launch_persist<64, true>(mw, a, (cudaStream_t)stream)
-                  : launch_persist<128, true>(mw, a, (cudaStream_t)stream);
+  // 2-D decomposition first (a quarter of the operand traffic per SM); the 1-D one when its clusters do not
+  // fit or B200RNN_BWD2D=0
+  static const bool twod = [] { const char* e = std::getenv("B200RNN_BWD2D"); return !(e && e[0] == '0'); }();
+  if (twod) {
+    rc = bm == 64 ? launch_persist<64, 2>(mw, a, (cudaStream_t)stream) : launch_persist<128, 2>(mw, a, (cudaStream_t)stream);
+    if (rc != B200RNN_EUNSUPPORTED) return rc;
+  }
+  return bm == 64 ? launch_persist<64, 1>(mw, a, (cudaStream_t)stream)
+                  : launch_persist<128, 1>(mw, a, (cudaStream_t)stream);
 }
 
 extern "C" int b200rnn_persist_status(int32_t* status) {
