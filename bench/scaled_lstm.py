@@ -13,7 +13,7 @@ from pathlib import Path
 import torch
 
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
-from pytorch_distributed_rnn_b200 import FusedLSTM  # noqa: E402
+from pytorch_distributed_rnn_b200 import FusedGRU, FusedLSTM  # noqa: E402
 
 
 def timed(fn, iters=3, warm=1):
@@ -36,11 +36,12 @@ def main():
     ap.add_argument("--seq", type=int, default=512)
     ap.add_argument("--input", type=int, default=9)
     ap.add_argument("--layers", type=int, default=2)
+    ap.add_argument("--cell", default="lstm", choices=["lstm", "gru"])
     a = ap.parse_args()
     torch.manual_seed(0)
     x = torch.randn(a.batch, a.seq, a.input, device="cuda")
-    ours = FusedLSTM(a.input, a.hidden, a.layers, batch_first=True).cuda()
-    stock = torch.nn.LSTM(a.input, a.hidden, a.layers, batch_first=True).cuda()
+    ours = (FusedLSTM if a.cell == "lstm" else FusedGRU)(a.input, a.hidden, a.layers, batch_first=True).cuda()
+    stock = (torch.nn.LSTM if a.cell == "lstm" else torch.nn.GRU)(a.input, a.hidden, a.layers, batch_first=True).cuda()
     stock.load_state_dict(ours.state_dict())
 
     def step_ours():
@@ -55,7 +56,7 @@ def main():
     flops = 0
     for l in range(a.layers):
         i = a.input if l == 0 else a.hidden
-        flops += 2 * 4 * a.hidden * (i + a.hidden) * a.seq * a.batch * 3   # fwd + 2x bwd
+        flops += 2 * (4 if a.cell == "lstm" else 3) * a.hidden * (i + a.hidden) * a.seq * a.batch * 3   # fwd + 2x bwd
     def fwd_ours():
         with torch.no_grad():
             ours(x)

@@ -9,7 +9,7 @@
 //
 // bf16 operands, fp32 accumulation / cell state (BASELINE.json config 4: "2-layer LSTM hidden=1024,
 // seq_len=512, bf16").  The whole time loop is driven from this file (one C call per direction).
-// Where the persistent kernels of rnn_persist.cu cover the shape (LSTM, H % 64 == 0, H / 8 <= #SMs,
+// Where the persistent kernels of rnn_persist.cu cover the shape (LSTM / GRU, H % 64 == 0, H / 8 <= #SMs,
 // B <= 128) the time loop of a layer is ONE cooperative launch with W_hh sharded across the SMs'
 // shared memory; otherwise it is the per-timestep formulation below (a GEMM + a cell kernel per step,
 // weights re-read from L2 each step).
@@ -26,6 +26,9 @@ extern "C" int64_t b200rnn_rnn_persist_stream_bytes(int32_t);
 extern "C" int b200rnn_lstm_persist_fwd(int32_t, int32_t, int32_t, float*, const void*, float*, float*, void*, void*, void*);
 extern "C" int b200rnn_lstm_persist_bwd(int32_t, int32_t, int32_t, const float*, const float*, const float*, const float*,
                                         const float*, const void*, float*, void*, void*, void*, void*);
+extern "C" int b200rnn_gru_persist_fwd(int32_t, int32_t, int32_t, float*, float*, const void*, const float*, float*, void*, void*, void*);
+extern "C" int b200rnn_gru_persist_bwd(int32_t, int32_t, int32_t, const float*, const float*, const float*, const float*,
+                                       const float*, const void*, float*, void*, float*, void*, void*, void*, void*);
 
 namespace b200rnn {
 namespace {
@@ -335,6 +338,9 @@ extern "C" int b200rnn_rnn_large_fwd(const b200rnn_model_desc* d, const float* p
       }
     } else {
       RC(b200rnn_gemm_bf16(xb, sc.wih_b, gates, params + d->off_bih[l], (int32_t)TB, G * H, inp8, inp8, inp8, G * H, 0, 0, stream));
+      if (b200rnn_rnn_persist_supported(d)) {
+        RC(b200rnn_gru_persist_fwd(T, B, H, gates, gh, sc.whh_b, params + d->off_bhh[l], h, sc.stream_img, sc.sync, stream));
+      } else
       for (int t = 0; t < T; ++t) {
         float* ght = gh + t * Bh * G;
         if (t > 0) RC(b200rnn_gemm_bf16(hb + (t - 1) * Bh, sc.whh_b, ght, params + d->off_bhh[l], B, G * H, H, H, H, G * H, 0, 0, stream));
@@ -396,6 +402,9 @@ extern "C" int b200rnn_rnn_large_bwd(const b200rnn_model_desc* d, const float* p
     if (lstm && b200rnn_rnn_persist_supported(d)) {
       RC(b200rnn_lstm_persist_bwd(T, B, H, gates, c, dh_ext, d_hn ? d_hn + l * Bh : nullptr, d_cn ? d_cn + l * Bh : nullptr,
                                   sc.whhT_b, sc.dG, sc.dG_b, sc.stream_img, sc.sync, stream));
+    } else if (!lstm && b200rnn_rnn_persist_supported(d)) {
+      RC(b200rnn_gru_persist_bwd(T, B, H, gates, gh, h, dh_ext, d_hn ? d_hn + l * Bh : nullptr, sc.whhT_b,
+                                 sc.dG, sc.dG_b, sc.dG2, sc.dG2_b, sc.stream_img, sc.sync, stream));
     } else
     for (int t = T - 1; t >= 0; --t) {
       const float* dhe = dh_ext ? dh_ext + t * Bh : nullptr;

@@ -141,8 +141,17 @@ __device__ __forceinline__ bf16* stream_unit(bf16* stream, int buf, int nk, int 
   return stream + (((size_t)buf * nk + chunk) * bm + row) * PK + ((j ^ (row & 7)) << 3);
 }
 
+// GRU notes (torch semantics n = tanh(x_n + r * (W_hn h + b_hn)), gate order r, z, n): `gates` is [T,B,3H]
+// (x-projection + b_ih in, activations r, z, n out), `gh` [T,B,3H] keeps hn = W_hn h + b_hn at [2H, 3H) for the
+// backward pass, the forward accumulator has a duplicate of gate n in the fourth 8-column group (N stays 32),
+// and the backward emits two gate-gradient sets: dGx = (dr, dz, dn) for the input-side GEMMs and
+// dGh = (dr, dz, dn * r) for the recurrent ones (dGh is what the next step streams).
 struct PersistArgs {
-  float* gates;          // fwd: [T,B,4H] input projection + bias in, gate activations out; bwd: activations in
+  float* gates;          // fwd: [T,B,G*H] input projection + bias in, gate activations out; bwd: activations in
+  float* gh;             // GRU: [T,B,3H]
+  const float* bhh;      // GRU fwd: b_hh [3H]
+  float* dG2;            // GRU bwd: dGh fp32 [T,B,3H]
+  bf16* dG2_b;           // GRU bwd: dGh bf16 [T,B,3H]
   float* c;              // [T,B,H]  fwd: out; bwd: in
   float* h;              // [T,B,H]  fwd: out
   bf16* stream;          // [2][K/64][BM][64] swizzled tile image of the streamed operand, by step parity
@@ -181,18 +190,20 @@ constexpr int NISS = 4;           // MMA-issuing warps: 1, 9, 10, 11 (one per K-
 constexpr int NTHREADS = 384;     // warps 4-7: epilogue (TMEM lane quarters 0-3)
 static_assert(NISS == PK / 16, "issuer i owns K-step i of every chunk");
 
-template <int BM, int MODE>
+template <int BM, int MODE, int CELL>
 __global__ void __launch_bounds__(NTHREADS, 1)
-lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs a) {
+rnn_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs a) {
   using Cfg = PersistCfg<BM, MODE>;
   constexpr int N = Cfg::N;
   constexpr bool BWD = Cfg::BWD, TWOD = Cfg::TWOD;
+  constexpr bool GRU = CELL == B200RNN_CELL_GRU;
+  constexpr int G = GRU ? 3 : 4;                        // gates
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int H = a.H, B = a.B, T = a.T;
-  const int KTOT = MODE == 1 ? 4 * H : H;              // K extent of this CTA's product
+  const int KTOT = MODE == 1 ? G * H : (MODE == 2 ? G * H / 4 : H);   // K extent of this CTA's product
   const int nk = KTOT / PK;
-  const int nk_img = (BWD ? 4 * H : H) / PK;           // chunks of the streamed operand's tile image
+  const int nk_img = (BWD ? G * H : H) / PK;           // chunks of the streamed operand's tile image
   const int ks = TWOD ? (int)(blockIdx.x & 3u) : 0;    // 2-D: rank in the cluster = K quarter
   const int ngi = (int)(blockIdx.x >> 2);              // 2-D: group of 32 output units
   const int ng = (nk + Cfg::CG - 1) / Cfg::CG;         // chunk groups per step
@@ -245,15 +256,15 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
         if (TWOD) {
 #pragma unroll
           for (int r = 0; r < 4; ++r)                                   // W_hh^T rows = my group's 32 units, my K quarter
-            tma_load_2d(sW + (size_t)kb * Cfg::W_CHUNK + r * (UC * PK * 2), &tma_w, wbar, ks * H + kb * PK, ngi * 32 + r * UC);
+            tma_load_2d(sW + (size_t)kb * Cfg::W_CHUNK + r * (UC * PK * 2), &tma_w, wbar, ks * KTOT + kb * PK, ngi * 32 + r * UC);
         } else if (BWD) {
 #pragma unroll
           for (int r = 0; r < N / UC; ++r)                                                  // W_hh^T rows = my units
             tma_load_2d(sW + (size_t)kb * Cfg::W_CHUNK + r * (UC * PK * 2), &tma_w, wbar, kb * PK, u0);
         } else {
 #pragma unroll
-          for (int g = 0; g < 4; ++g)                                                       // W_hh rows g*H + my units
-            tma_load_2d(sW + (size_t)kb * Cfg::W_CHUNK + g * (UC * PK * 2), &tma_w, wbar, kb * PK, g * H + u0);
+          for (int g = 0; g < 4; ++g)                                   // W_hh rows g*H + my units (GRU: gate n twice)
+            tma_load_2d(sW + (size_t)kb * Cfg::W_CHUNK + g * (UC * PK * 2), &tma_w, wbar, kb * PK, (g < G ? g : G - 1) * H + u0);
         }
       }
     }
@@ -330,7 +341,14 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
     float carry[UC];   // fwd: c_{t-1}; bwd: dc flowing into step t
 #pragma unroll
     for (int i = 0; i < UC; ++i) carry[i] = 0.0f;
-    if (BWD && live && a.d_cn != nullptr) {
+    float bh[3][UC];   // GRU forward: b_hh of my units
+    if (GRU && !BWD) {
+#pragma unroll
+      for (int g = 0; g < 3; ++g)
+#pragma unroll
+        for (int i = 0; i < UC; ++i) bh[g][i] = a.bhh[g * H + u0 + i];
+    }
+    if (!GRU && BWD && live && a.d_cn != nullptr) {
 #pragma unroll
       for (int i = 0; i < UC; ++i) carry[i] = a.d_cn[(int64_t)row * H + u0 + i];
     }
@@ -345,15 +363,22 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
       float4 cv[2], cpv[2];
       if (live) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const float4* gp = reinterpret_cast<const float4*>(a.gates + rb * 4 * H + (int64_t)g * H + u0);
+        for (int g = 0; g < G; ++g) {
+          const float4* gp = reinterpret_cast<const float4*>(a.gates + rb * G * H + (int64_t)g * H + u0);
           gv[g][0] = gp[0]; gv[g][1] = gp[1];
         }
+        if (GRU) gv[3][0] = gv[3][1] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (BWD) {
-          const float4* cp = reinterpret_cast<const float4*>(a.c + rb * H + u0);
-          cv[0] = cp[0]; cv[1] = cp[1];
+          if (GRU) {   // gv[3] = hn; cpv = h_{t-1}; cv unused
+            const float4* hp = reinterpret_cast<const float4*>(a.gh + rb * 3 * H + 2 * (int64_t)H + u0);
+            gv[3][0] = hp[0]; gv[3][1] = hp[1];
+            cv[0] = cv[1] = make_float4(0.f, 0.f, 0.f, 0.f);
+          } else {
+            const float4* cp = reinterpret_cast<const float4*>(a.c + rb * H + u0);
+            cv[0] = cp[0]; cv[1] = cp[1];
+          }
           if (t > 0) {
-            const float4* pp = reinterpret_cast<const float4*>(a.c + (rb - B) * H + u0);
+            const float4* pp = reinterpret_cast<const float4*>((GRU ? a.h : a.c) + (rb - B) * H + u0);
             cpv[0] = pp[0]; cpv[1] = pp[1];
           } else {
             cpv[0] = cpv[1] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -447,14 +472,25 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
         if (live) {
 #pragma unroll
           for (int i = 0; i < UC; ++i) {
-            const float ig = sigmoid_f(gin[0][i] + acc[(0 * UC + i) % N]);
-            const float fg = sigmoid_f(gin[1][i] + acc[(1 * UC + i) % N]);
-            const float gg = tanh_f(gin[2][i] + acc[(2 * UC + i) % N]);
-            const float og = sigmoid_f(gin[3][i] + acc[(3 * UC + i) % N]);
-            const float cc = fmaf(fg, carry[i], ig * gg);
-            carry[i] = cc;
-            hv[i] = og * tanh_f(cc);
-            go[0][i] = ig; go[1][i] = fg; go[2][i] = gg; go[3][i] = og;
+            if constexpr (!GRU) {
+              const float ig = sigmoid_f(gin[0][i] + acc[(0 * UC + i) % N]);
+              const float fg = sigmoid_f(gin[1][i] + acc[(1 * UC + i) % N]);
+              const float gg = tanh_f(gin[2][i] + acc[(2 * UC + i) % N]);
+              const float og = sigmoid_f(gin[3][i] + acc[(3 * UC + i) % N]);
+              const float cc = fmaf(fg, carry[i], ig * gg);
+              carry[i] = cc;
+              hv[i] = og * tanh_f(cc);
+              go[0][i] = ig; go[1][i] = fg; go[2][i] = gg; go[3][i] = og;
+            } else {
+              // carry = h_{t-1}; go[3] = hn, stashed for the backward pass
+              const float rg = sigmoid_f(gin[0][i] + acc[(0 * UC + i) % N] + bh[0][i]);
+              const float zg = sigmoid_f(gin[1][i] + acc[(1 * UC + i) % N] + bh[1][i]);
+              const float hn = acc[(2 * UC + i) % N] + bh[2][i];
+              const float ng = tanh_f(fmaf(rg, hn, gin[2][i]));
+              hv[i] = fmaf(zg, carry[i] - ng, ng);
+              carry[i] = hv[i];
+              go[0][i] = rg; go[1][i] = zg; go[2][i] = ng; go[3][i] = hn;
+            }
           }
           // the operand of the next step first ...
           __nv_bfloat162 p0 = __floats2bfloat162_rn(hv[0], hv[1]), p1 = __floats2bfloat162_rn(hv[2], hv[3]);
@@ -474,14 +510,21 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
         // ... then the stash for the backward pass, off the critical path
         if (live) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float4* gp = reinterpret_cast<float4*>(a.gates + rb * 4 * H + (int64_t)g * H + u0);
+          for (int g = 0; g < G; ++g) {
+            float4* gp = reinterpret_cast<float4*>(a.gates + rb * G * H + (int64_t)g * H + u0);
             gp[0] = make_float4(go[g][0], go[g][1], go[g][2], go[g][3]);
             gp[1] = make_float4(go[g][4], go[g][5], go[g][6], go[g][7]);
           }
-          float4* cp = reinterpret_cast<float4*>(a.c + rb * H + u0);
-          cp[0] = make_float4(carry[0], carry[1], carry[2], carry[3]);
-          cp[1] = make_float4(carry[4], carry[5], carry[6], carry[7]);
+          // LSTM: c_t; GRU: hn into gh[:, 2H + u]
+          float4* cp = GRU ? reinterpret_cast<float4*>(a.gh + rb * 3 * H + 2 * (int64_t)H + u0)
+                           : reinterpret_cast<float4*>(a.c + rb * H + u0);
+          if constexpr (GRU) {
+            cp[0] = make_float4(go[3][0], go[3][1], go[3][2], go[3][3]);
+            cp[1] = make_float4(go[3][4], go[3][5], go[3][6], go[3][7]);
+          } else {
+            cp[0] = make_float4(carry[0], carry[1], carry[2], carry[3]);
+            cp[1] = make_float4(carry[4], carry[5], carry[6], carry[7]);
+          }
           float4* hp = reinterpret_cast<float4*>(a.h + rb * H + u0);
           hp[0] = make_float4(hv[0], hv[1], hv[2], hv[3]);
           hp[1] = make_float4(hv[4], hv[5], hv[6], hv[7]);
@@ -495,18 +538,31 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
           const float dhe[UC] = {aux[0].x, aux[0].y, aux[0].z, aux[0].w, aux[1].x, aux[1].y, aux[1].z, aux[1].w};
 #pragma unroll
           for (int i = 0; i < UC; ++i) {
-            const float ig = gin[0][i], fg = gin[1][i], gg = gin[2][i], og = gin[3][i];
-            const float dh = dhe[i] + dhrec[i];
-            const float tc = tanh_f(cvv[i]);
-            const float dct = fmaf(dh * og, 1.0f - tc * tc, carry[i]);
-            dg[0][i] = dct * gg * ig * (1.0f - ig);
-            dg[1][i] = dct * cpp[i] * fg * (1.0f - fg);
-            dg[2][i] = dct * ig * (1.0f - gg * gg);
-            dg[3][i] = dh * tc * og * (1.0f - og);
-            carry[i] = dct * fg;
+            if constexpr (!GRU) {
+              const float ig = gin[0][i], fg = gin[1][i], gg = gin[2][i], og = gin[3][i];
+              const float dh = dhe[i] + dhrec[i];
+              const float tc = tanh_f(cvv[i]);
+              const float dct = fmaf(dh * og, 1.0f - tc * tc, carry[i]);
+              dg[0][i] = dct * gg * ig * (1.0f - ig);
+              dg[1][i] = dct * cpp[i] * fg * (1.0f - fg);
+              dg[2][i] = dct * ig * (1.0f - gg * gg);
+              dg[3][i] = dh * tc * og * (1.0f - og);
+              carry[i] = dct * fg;
+            } else {
+              // carry = dh_t * z_t flowing straight into h_{t-1}; dg[0..2] = dGh (dr, dz, dn * r), dg[3] = dn
+              const float rg = gin[0][i], zg = gin[1][i], ng = gin[2][i], hn = gin[3][i];
+              const float dh = dhe[i] + dhrec[i] + carry[i];
+              const float dn = dh * (1.0f - zg) * (1.0f - ng * ng);
+              dg[0][i] = dn * hn * rg * (1.0f - rg);
+              dg[1][i] = dh * (cpp[i] - ng) * zg * (1.0f - zg);
+              dg[2][i] = dn * rg;
+              dg[3][i] = dn;
+              carry[i] = dh * zg;
+              (void)cvv;
+            }
           }
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
+          for (int g = 0; g < G; ++g) {
             __nv_bfloat162 p0 = __floats2bfloat162_rn(dg[g][0], dg[g][1]), p1 = __floats2bfloat162_rn(dg[g][2], dg[g][3]);
             __nv_bfloat162 p2 = __floats2bfloat162_rn(dg[g][4], dg[g][5]), p3 = __floats2bfloat162_rn(dg[g][6], dg[g][7]);
             uint4 pk;
@@ -523,11 +579,26 @@ lstm_persist_kernel(const __grid_constant__ CUtensorMap tma_w, const PersistArgs
         PSTAMP(20);
         if (live) {
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            float4* gp = reinterpret_cast<float4*>(a.dG + rb * 4 * H + (int64_t)g * H + u0);
+          for (int g = 0; g < G; ++g) {
+            // LSTM: dG; GRU: dGh (what was streamed) into dG2 and dGx = (dr, dz, dn) into dG
+            float* d32 = GRU ? a.dG2 : a.dG;
+            bf16* d16 = GRU ? a.dG2_b : a.dG_b;
+            float4* gp = reinterpret_cast<float4*>(d32 + rb * G * H + (int64_t)g * H + u0);
             gp[0] = make_float4(dg[g][0], dg[g][1], dg[g][2], dg[g][3]);
             gp[1] = make_float4(dg[g][4], dg[g][5], dg[g][6], dg[g][7]);
-            *reinterpret_cast<uint4*>(a.dG_b + rb * 4 * H + (int64_t)g * H + u0) = dgp[g];
+            *reinterpret_cast<uint4*>(d16 + rb * G * H + (int64_t)g * H + u0) = dgp[g];
+            if constexpr (GRU) {
+              const int gs = g == 2 ? 3 : g;   // dGx differs from dGh only in the n gate (dn instead of dn * r)
+              float4* xp = reinterpret_cast<float4*>(a.dG + rb * G * H + (int64_t)g * H + u0);
+              xp[0] = make_float4(dg[gs][0], dg[gs][1], dg[gs][2], dg[gs][3]);
+              xp[1] = make_float4(dg[gs][4], dg[gs][5], dg[gs][6], dg[gs][7]);
+              __nv_bfloat162 p0 = __floats2bfloat162_rn(dg[gs][0], dg[gs][1]), p1 = __floats2bfloat162_rn(dg[gs][2], dg[gs][3]);
+              __nv_bfloat162 p2 = __floats2bfloat162_rn(dg[gs][4], dg[gs][5]), p3 = __floats2bfloat162_rn(dg[gs][6], dg[gs][7]);
+              uint4 pk;
+              pk.x = *reinterpret_cast<uint32_t*>(&p0); pk.y = *reinterpret_cast<uint32_t*>(&p1);
+              pk.z = *reinterpret_cast<uint32_t*>(&p2); pk.w = *reinterpret_cast<uint32_t*>(&p3);
+              *reinterpret_cast<uint4*>(a.dG_b + rb * G * H + (int64_t)g * H + u0) = pk;
+            }
           }
         }
       }
@@ -569,11 +640,13 @@ constexpr size_t kSmemLimit = 227 * 1024;
 constexpr size_t kSmemFixed = 2 * MAX_STAGES * 8 + 64 + 1024;   // barriers + slots + alignment slack
 constexpr int kMinStages = 2;
 
+inline int persist_nk(int mode, int H, int G) { return (mode == 1 ? G * H : (mode == 2 ? G * H / 4 : H)) / PK; }
+
 // ring depth: the whole streamed operand of a step if it fits next to the weight shard, else what does
 template <int BM, int MODE>
-int persist_stages(int H) {
+int persist_stages(int H, int G) {
   using Cfg = PersistCfg<BM, MODE>;
-  const int nk = (MODE == 1 ? 4 * H : H) / PK;
+  const int nk = persist_nk(MODE, H, G);
   const int ng = (nk + Cfg::CG - 1) / Cfg::CG;
   const size_t w = (size_t)nk * Cfg::W_CHUNK + Cfg::XBUF;
   if (w + kSmemFixed + (size_t)kMinStages * Cfg::STAGE > kSmemLimit) return 0;
@@ -583,20 +656,22 @@ int persist_stages(int H) {
   return st;
 }
 template <int BM, int MODE>
-size_t persist_smem(int H) {
+size_t persist_smem(int H, int G) {
   using Cfg = PersistCfg<BM, MODE>;
-  const int nk = (MODE == 1 ? 4 * H : H) / PK;
-  return (size_t)nk * Cfg::W_CHUNK + (size_t)persist_stages<BM, MODE>(H) * Cfg::STAGE + Cfg::XBUF + kSmemFixed;
+  return (size_t)persist_nk(MODE, H, G) * Cfg::W_CHUNK + (size_t)persist_stages<BM, MODE>(H, G) * Cfg::STAGE + Cfg::XBUF + kSmemFixed;
 }
 
 // Returns B200RNN_EUNSUPPORTED (without launching) when the grid cannot be made co-resident, so that the
 // caller can fall back to another decomposition.
-template <int BM, int MODE>
+template <int BM, int MODE, int CELL>
 int launch_persist(const CUtensorMap& mw, PersistArgs a, cudaStream_t s) {
-  a.stages = persist_stages<BM, MODE>(a.H);
+  constexpr int G = CELL == B200RNN_CELL_GRU ? 3 : 4;
+  B200_REQUIRE(MODE != 2 || (G * a.H) % (4 * PK) == 0, B200RNN_EUNSUPPORTED,
+               "rnn_persist: K = %d does not split into four 64-aligned quarters", G * a.H);
+  a.stages = persist_stages<BM, MODE>(a.H, G);
   B200_REQUIRE(a.stages >= kMinStages, B200RNN_EUNSUPPORTED, "rnn_persist: weight shard of H=%d leaves no room for the operand ring", a.H);
-  const size_t smem = persist_smem<BM, MODE>(a.H);
-  auto kern = lstm_persist_kernel<BM, MODE>;
+  const size_t smem = persist_smem<BM, MODE>(a.H, G);
+  auto kern = rnn_persist_kernel<BM, MODE, CELL>;
   B200_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = a.H / UC;
   cudaLaunchConfig_t cfg = {};
@@ -632,46 +707,60 @@ int launch_persist(const CUtensorMap& mw, PersistArgs a, cudaStream_t s) {
   return B200RNN_OK;
 }
 
+template <int CELL>
+int run_fwd(const CUtensorMap& mw, const PersistArgs& a, cudaStream_t s) {
+  return a.B <= 64 ? launch_persist<64, 0, CELL>(mw, a, s) : launch_persist<128, 0, CELL>(mw, a, s);
+}
+// 2-D decomposition first (a quarter of the operand traffic per SM); the 1-D one when K does not split, its
+// clusters do not fit, or B200RNN_BWD2D=0
+template <int CELL>
+int run_bwd(const CUtensorMap& mw, const PersistArgs& a, cudaStream_t s) {
+  static const bool twod = [] { const char* e = std::getenv("B200RNN_BWD2D"); return !(e && e[0] == '0'); }();
+  if (twod) {
+    const int rc = a.B <= 64 ? launch_persist<64, 2, CELL>(mw, a, s) : launch_persist<128, 2, CELL>(mw, a, s);
+    if (rc != B200RNN_EUNSUPPORTED) return rc;
+  }
+  return a.B <= 64 ? launch_persist<64, 1, CELL>(mw, a, s) : launch_persist<128, 1, CELL>(mw, a, s);
+}
+
 }  // namespace
 }  // namespace b200rnn
 
 using namespace b200rnn;
 
-// Shapes the persistent kernels cover: LSTM, H a multiple of 64 with H/8 CTAs co-resident (one per
+// Shapes the persistent kernels cover: LSTM / GRU, H a multiple of 64 with H/8 CTAs co-resident (one per
 // SM), batch <= 128, and a weight shard + ring that fits shared memory.  B200RNN_PERSIST=0 disables.
 extern "C" int b200rnn_rnn_persist_supported(const b200rnn_model_desc* d) {
-  if (d == nullptr || d->cell != B200RNN_CELL_LSTM) return 0;
+  if (d == nullptr || (d->cell != B200RNN_CELL_LSTM && d->cell != B200RNN_CELL_GRU)) return 0;
   static const bool enabled = [] { const char* e = std::getenv("B200RNN_PERSIST"); return !(e && e[0] == '0'); }();
   if (!enabled) return 0;
-  const int H = d->hidden_size, B = d->batch;
+  const int H = d->hidden_size, B = d->batch, G = d->cell == B200RNN_CELL_LSTM ? 4 : 3;
   if (H % 64 != 0 || H < 64 || B < 1 || B > 128 || d->seq_len < 1) return 0;
   if (H / UC > num_sms()) return 0;
-  const int st = B <= 64 ? (persist_stages<64, 1>(H) < persist_stages<64, 0>(H) ? persist_stages<64, 1>(H) : persist_stages<64, 0>(H))
-                         : (persist_stages<128, 1>(H) < persist_stages<128, 0>(H) ? persist_stages<128, 1>(H) : persist_stages<128, 0>(H));
+  const int st = B <= 64 ? (persist_stages<64, 1>(H, G) < persist_stages<64, 0>(H, G) ? persist_stages<64, 1>(H, G) : persist_stages<64, 0>(H, G))
+                         : (persist_stages<128, 1>(H, G) < persist_stages<128, 0>(H, G) ? persist_stages<128, 1>(H, G) : persist_stages<128, 0>(H, G));
   return st >= kMinStages ? 1 : 0;
 }
 
 // Bytes of the double-buffered tile image of the streamed operand (backward: K = 4H, up to 128 rows).
 extern "C" int64_t b200rnn_rnn_persist_stream_bytes(int32_t H) { return 2ll * (4 * H / PK) * 128 * PK * 2; }
 
-// Forward time loop of one layer.  gates: [T,B,4H] fp32 holding x-projection + biases (overwritten with
+// Forward time loop of one LSTM layer.  gates: [T,B,4H] fp32 holding x-projection + biases (overwritten with
 // the gate activations); whh_b: bf16 [4H,H]; outputs c, h (fp32), both [T,B,H]; stream: scratch of
 // b200rnn_rnn_persist_stream_bytes(H); sync: 256 bytes.
 extern "C" int b200rnn_lstm_persist_fwd(int32_t T, int32_t B, int32_t H, float* gates, const void* whh_b,
                                         float* c, float* h, void* stream_buf, void* sync, void* stream) {
   B200_REQUIRE(gates && whh_b && c && h && stream_buf && sync, B200RNN_EINVAL, "lstm_persist_fwd: null argument");
   CUtensorMap mw;
-  const int bm = B <= 64 ? 64 : 128;
   int rc = make_map_weight(&mw, whh_b, 4 * H, H);
   if (rc) return rc;
   PersistArgs a{};
   a.gates = gates; a.c = c; a.h = h; a.stream = (bf16*)stream_buf; a.sync = (PersistSync*)sync;
   a.B = B; a.H = H; a.T = T;
-  return bm == 64 ? launch_persist<64, 0>(mw, a, (cudaStream_t)stream)
-                  : launch_persist<128, 0>(mw, a, (cudaStream_t)stream);
+  return run_fwd<B200RNN_CELL_LSTM>(mw, a, (cudaStream_t)stream);
 }
 
-// Backward time loop of one layer.  gates / c: the forward stash; dh_ext: [T,B,H] gradient from above
+// Backward time loop of one LSTM layer.  gates / c: the forward stash; dh_ext: [T,B,H] gradient from above
 // (nullable); d_hn / d_cn: [B,H] (nullable); whhT_b: bf16 [H,4H] (W_hh transposed); outputs dG fp32 and
 // dG_b bf16, both [T,B,4H] row-major.
 extern "C" int b200rnn_lstm_persist_bwd(int32_t T, int32_t B, int32_t H, const float* gates, const float* c,
@@ -680,7 +769,6 @@ extern "C" int b200rnn_lstm_persist_bwd(int32_t T, int32_t B, int32_t H, const f
                                         void* stream) {
   B200_REQUIRE(gates && c && whhT_b && dG && dG_b && stream_buf && sync, B200RNN_EINVAL, "lstm_persist_bwd: null argument");
   CUtensorMap mw;
-  const int bm = B <= 64 ? 64 : 128;
   int rc = make_map_weight(&mw, whhT_b, H, 4 * H);
   if (rc) return rc;
   PersistArgs a{};
@@ -688,15 +776,39 @@ extern "C" int b200rnn_lstm_persist_bwd(int32_t T, int32_t B, int32_t H, const f
   a.dh_ext = dh_ext; a.d_hn = d_hn; a.d_cn = d_cn; a.dG = dG; a.dG_b = (bf16*)dG_b;
   a.stream = (bf16*)stream_buf; a.sync = (PersistSync*)sync;
   a.B = B; a.H = H; a.T = T;
-  // 2-D decomposition first (a quarter of the operand traffic per SM); the 1-D one when its clusters do not
-  // fit or B200RNN_BWD2D=0
-  static const bool twod = [] { const char* e = std::getenv("B200RNN_BWD2D"); return !(e && e[0] == '0'); }();
-  if (twod) {
-    rc = bm == 64 ? launch_persist<64, 2>(mw, a, (cudaStream_t)stream) : launch_persist<128, 2>(mw, a, (cudaStream_t)stream);
-    if (rc != B200RNN_EUNSUPPORTED) return rc;
-  }
-  return bm == 64 ? launch_persist<64, 1>(mw, a, (cudaStream_t)stream)
-                  : launch_persist<128, 1>(mw, a, (cudaStream_t)stream);
+  return run_bwd<B200RNN_CELL_LSTM>(mw, a, (cudaStream_t)stream);
+}
+
+// GRU forward time loop of one layer.  gates: [T,B,3H] x-projection + b_ih in, (r, z, n) out; gh: [T,B,3H],
+// receives hn at [2H, 3H); whh_b: bf16 [3H,H]; bhh: fp32 [3H]; h: [T,B,H] out.
+extern "C" int b200rnn_gru_persist_fwd(int32_t T, int32_t B, int32_t H, float* gates, float* gh, const void* whh_b,
+                                       const float* bhh, float* h, void* stream_buf, void* sync, void* stream) {
+  B200_REQUIRE(gates && gh && whh_b && bhh && h && stream_buf && sync, B200RNN_EINVAL, "gru_persist_fwd: null argument");
+  CUtensorMap mw;
+  int rc = make_map_weight(&mw, whh_b, 3 * H, H);
+  if (rc) return rc;
+  PersistArgs a{};
+  a.gates = gates; a.gh = gh; a.bhh = bhh; a.h = h; a.stream = (bf16*)stream_buf; a.sync = (PersistSync*)sync;
+  a.B = B; a.H = H; a.T = T;
+  return run_fwd<B200RNN_CELL_GRU>(mw, a, (cudaStream_t)stream);
+}
+
+// GRU backward time loop of one layer.  gates / gh / h: the forward stash; whhT_b: bf16 [H,3H]; outputs
+// dGx = (dr, dz, dn) in dG / dG_b and dGh = (dr, dz, dn * r) in dG2 / dG2_b, all [T,B,3H] row-major.
+extern "C" int b200rnn_gru_persist_bwd(int32_t T, int32_t B, int32_t H, const float* gates, const float* gh, const float* h,
+                                       const float* dh_ext, const float* d_hn, const void* whhT_b, float* dG, void* dG_b,
+                                       float* dG2, void* dG2_b, void* stream_buf, void* sync, void* stream) {
+  B200_REQUIRE(gates && gh && h && whhT_b && dG && dG_b && dG2 && dG2_b && stream_buf && sync, B200RNN_EINVAL,
+               "gru_persist_bwd: null argument");
+  CUtensorMap mw;
+  int rc = make_map_weight(&mw, whhT_b, H, 3 * H);
+  if (rc) return rc;
+  PersistArgs a{};
+  a.gates = const_cast<float*>(gates); a.gh = const_cast<float*>(gh); a.h = const_cast<float*>(h);
+  a.dh_ext = dh_ext; a.d_hn = d_hn; a.dG = dG; a.dG_b = (bf16*)dG_b; a.dG2 = dG2; a.dG2_b = (bf16*)dG2_b;
+  a.stream = (bf16*)stream_buf; a.sync = (PersistSync*)sync;
+  a.B = B; a.H = H; a.T = T;
+  return run_bwd<B200RNN_CELL_GRU>(mw, a, (cudaStream_t)stream);
 }
 
 extern "C" int b200rnn_persist_status(int32_t* status) {

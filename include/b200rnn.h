@@ -232,7 +232,7 @@ int b200rnn_rnn_large_bwd(const b200rnn_model_desc* d, const float* params, cons
 /* Persistent time loops of the large-hidden LSTM (csrc/rnn/rnn_persist.cu): one cooperative launch
  * per layer and direction, W_hh sharded across the SMs' shared memory, h_t / dG_t exchanged through
  * L2 with a grid barrier per step.  b200rnn_rnn_large_fwd/bwd use them automatically when
- * b200rnn_rnn_persist_supported(d) (LSTM, hidden % 64 == 0, hidden / 8 <= #SMs, batch <= 128;
+ * b200rnn_rnn_persist_supported(d) (LSTM / GRU, hidden % 64 == 0, hidden / 8 <= #SMs, batch <= 128;
  * B200RNN_PERSIST=0 disables).  `sync` is 256 bytes of device memory, zeroed by the call.
  * b200rnn_persist_status() returns non-zero after a bounded wait inside the kernels timed out. */
 int b200rnn_rnn_persist_supported(const b200rnn_model_desc* d);
@@ -243,6 +243,14 @@ int b200rnn_lstm_persist_bwd(int32_t T, int32_t B, int32_t H, const float* gates
                              const float* dh_ext, const float* d_hn, const float* d_cn,
                              const void* whhT_bf16, float* dG, void* dG_bf16, void* stream_img, void* sync,
                              void* stream);
+/* GRU members: gates [T,B,3H] (x-projection + b_ih in, r / z / n out), gh [T,B,3H] (receives
+ * W_hn h + b_hn at [2H,3H)), bhh fp32 [3H]; the backward writes dGx = (dr, dz, dn) to dG / dG_bf16 and
+ * dGh = (dr, dz, dn*r) to dG2 / dG2_bf16. */
+int b200rnn_gru_persist_fwd(int32_t T, int32_t B, int32_t H, float* gates, float* gh, const void* whh_bf16,
+                            const float* bhh, float* h, void* stream_img, void* sync, void* stream);
+int b200rnn_gru_persist_bwd(int32_t T, int32_t B, int32_t H, const float* gates, const float* gh, const float* h,
+                            const float* dh_ext, const float* d_hn, const void* whhT_bf16, float* dG,
+                            void* dG_bf16, float* dG2, void* dG2_bf16, void* stream_img, void* sync, void* stream);
 int b200rnn_persist_status(int32_t* status);
 
 /* ---- L2 flush helper for benchmarking (writes `bytes` of scratch). */

@@ -23,6 +23,9 @@ def _rel(a, b):
     (FusedGRU, nn.GRU, 9, 64, 2, 24, 12),
     (FusedGRU, nn.GRU, 9, 40, 2, 16, 10),      # H % 8 == 0 but outside the fused small-hidden family
     (FusedGRU, nn.GRU, 48, 128, 1, 8, 7),
+    (FusedGRU, nn.GRU, 24, 256, 2, 80, 9),     # persistent GRU, 2-D backward (3H % 256 == 0), M = 128 variants
+    (FusedGRU, nn.GRU, 16, 1024, 1, 64, 5),    # persistent GRU at the scaled geometry
+    (FusedGRU, nn.GRU, 16, 192, 1, 130, 4),    # B > 128: per-timestep formulation
 ])
 def test_large_path_forward_backward(cls, stock, I, H, L, B, T):
     torch.manual_seed(H + T)
