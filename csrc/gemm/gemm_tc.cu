@@ -30,8 +30,10 @@ using namespace tc;
 
 constexpr int BM = 128, BK = 64, STAGES = 4;
 constexpr int TILE_BYTES = BM * BK * 2;           // 16 KiB for the A tile per stage
-// BN = 128 for square-ish problems; BN = 32 for skinny ones (M <= 128: the per-timestep recurrent
-// projection h[B,H] x W_hh^T) so that N / 32 CTAs cover the SMs instead of N / 128.
+// BN = 256 for large problems: one thread issues a tcgen05.mma every ~129 cycles whatever its shape
+// (profiles/r1_microbench_tma_mma.md), so only a 128x256 MMA (128 cycles of tensor time) keeps the tensor core
+// busy from a single issuer; BN = 128 when N or the grid is too small for that; BN = 32 for skinny problems
+// (M <= 128: the per-timestep recurrent projection h[B,H] x W_hh^T) so that N / 32 CTAs cover the SMs.
 template <int BN> constexpr int smem_bytes() { return STAGES * (TILE_BYTES + BN * BK * 2) + 256 + 1024; }
 
 __device__ int g_gemm_error = 0;
@@ -208,7 +210,9 @@ extern "C" int b200rnn_gemm_bf16(const void* A, const void* B, void* C, const fl
                                  int32_t c_is_bf16, void* stream) {
   B200_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, B200RNN_EINVAL, "gemm_bf16: bad argument");
   const bool skinny = (M <= BM) && ((N + 127) / 128 < num_sms() / 2) && N >= 32;
-  const int bn = skinny ? 32 : 128;
+  const int64_t ctas256 = (int64_t)((N + 255) / 256) * ((M + BM - 1) / BM);
+  const bool wide = !skinny && N >= 256 && ctas256 >= num_sms() / 2;
+  const int bn = skinny ? 32 : (wide ? 256 : 128);
   CUtensorMap ma, mb;
   int rc = make_map(&ma, A, M, K, lda, BM, "A");
   if (rc) return rc;
@@ -218,10 +222,12 @@ extern "C" int b200rnn_gemm_bf16(const void* A, const void* B, void* C, const fl
   if (!attr_set) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<128>()));
     B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<32>()));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes<256>()));
     attr_set = true;
   }
   dim3 grid((N + bn - 1) / bn, (M + BM - 1) / BM);
   if (skinny) gemm_bf16_kernel<32><<<grid, 256, smem_bytes<32>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16);
+  else if (wide) gemm_bf16_kernel<256><<<grid, 256, smem_bytes<256>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16);
   else gemm_bf16_kernel<128><<<grid, 256, smem_bytes<128>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16);
   B200_CHECK_LAUNCH();
   return B200RNN_OK;
