@@ -206,3 +206,17 @@ extern "C" int b200rnn_l2_flush(void* scratch, int64_t bytes, void* stream) {
   B200_CHECK_LAUNCH();
   return B200RNN_OK;
 }
+
+// Non-zero once a bounded wait of the layer-wavefront kernels (csrc/rnn/lstm_small.inc) timed out.
+extern "C" int b200rnn_wave_status_lstm_fwd(void);
+extern "C" int b200rnn_wave_status_lstm_bwd(void);
+extern "C" int b200rnn_wave_status_lstm_bwd_dx(void);
+extern "C" int b200rnn_wave_status_gru_fwd(void);
+extern "C" int b200rnn_wave_status_gru_bwd(void);
+extern "C" int b200rnn_wave_status_gru_bwd_dx(void);
+extern "C" int b200rnn_wave_status(int32_t* status) {
+  B200_REQUIRE(status != nullptr, B200RNN_EINVAL, "wave_status: null");
+  *status = b200rnn_wave_status_lstm_fwd() | b200rnn_wave_status_lstm_bwd() | b200rnn_wave_status_lstm_bwd_dx() |
+            b200rnn_wave_status_gru_fwd() | b200rnn_wave_status_gru_bwd() | b200rnn_wave_status_gru_bwd_dx();
+  return B200RNN_OK;
+}

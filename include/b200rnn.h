@@ -253,6 +253,11 @@ int b200rnn_gru_persist_bwd(int32_t T, int32_t B, int32_t H, const float* gates,
                             void* dG_bf16, float* dG2, void* dG2_bf16, void* stream_img, void* sync, void* stream);
 int b200rnn_persist_status(int32_t* status);
 
+/* Non-zero once a bounded wait of the small-hidden family's layer-wavefront mode timed out (a
+ * consumer CTA never saw its producer's values; results of that call are then garbage).
+ * B200RNN_WAVE=0 keeps the layers of a batch tile in one CTA, in sequence. */
+int b200rnn_wave_status(int32_t* status);
+
 /* ---- L2 flush helper for benchmarking (writes `bytes` of scratch). */
 int b200rnn_l2_flush(void* scratch, int64_t bytes, void* stream);
 

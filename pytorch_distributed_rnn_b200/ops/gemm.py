@@ -63,3 +63,11 @@ def persist_status() -> int:
     st = C.c_int32(0)
     _native.check(_native.lib().b200rnn_persist_status(C.byref(st)), "persist_status")
     return st.value
+
+
+def wave_status() -> int:
+    """Non-zero once a bounded wait of the small-hidden layer-wavefront kernels (csrc/rnn/lstm_small.inc) timed out."""
+    import ctypes as C
+    st = C.c_int32(0)
+    _native.check(_native.lib().b200rnn_wave_status(C.byref(st)), "wave_status")
+    return st.value

@@ -151,3 +151,25 @@ def test_engine_trains_a_gru_motion_model(B, T, L):
         want_loss = nn.functional.cross_entropy(out, ys[0], reduction="sum").item()
     got = eng.evaluate(xs[0].to(DEV), ys[0].to(DEV)).cpu()
     assert abs(float(got[0]) - want_loss) < 2e-3 * max(1.0, want_loss / 100)
+
+
+@pytest.mark.parametrize("cell", ["lstm", "gru"])
+@pytest.mark.parametrize("B,T,L", [(180, 128, 2), (90, 40, 3), (360, 64, 2)])
+def test_layer_wavefront_shapes(cell, B, T, L):
+    """Per-rank batches of the 8 / 4-GPU strong-scaling runs: few tiles, so the layers of a tile run concurrently on
+    different SMs (sentinel hand-off through global memory).  Forward, every gradient and the watchdog flag."""
+    from pytorch_distributed_rnn_b200.ops.gemm import wave_status
+    torch.manual_seed(B + L)
+    m = (FusedGRU if cell == "gru" else FusedLSTM)(9, 32, L, batch_first=True).to(DEV)
+    ref = _stock(m)
+    x = torch.randn(B, T, 9)
+    wo = torch.randn(B, T, 32)
+    for _ in range(2):   # twice: the second call reuses cached allocations holding stale (non-sentinel) values
+        m.zero_grad()
+        out = m(x.to(DEV))[0]
+        (out * wo.to(DEV)).sum().backward()
+    ro = ref(x)[0]
+    (ro * wo).sum().backward()
+    assert torch.allclose(out.detach().cpu(), ro.detach(), atol=2e-5, rtol=1e-4)
+    _assert_grads_close(m, ref)
+    assert wave_status() == 0
