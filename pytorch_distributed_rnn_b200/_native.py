@@ -172,6 +172,29 @@ def lib() -> C.CDLL:
     return load(required=True)
 
 
+def device_status() -> dict:
+    """Watchdog words of the kernels with bounded in-kernel waits (synchronises the device): the tcgen05 GEMM
+    pipeline, the persistent large-hidden time loops and the small-hidden layer wavefront.  All zero = healthy."""
+    out = {}
+    l = lib()
+    for name in ("gemm", "persist", "wave", "tc"):
+        fn = getattr(l, f"b200rnn_{name}_status", None)
+        if fn is None:
+            continue
+        st = C.c_int32(0)
+        check(fn(C.byref(st)), f"{name}_status")
+        out[name] = st.value
+    return out
+
+
+def assert_device_healthy() -> None:
+    """Raise if any in-kernel watchdog fired since the library was loaded (results of that call are garbage)."""
+    bad = {k: v for k, v in device_status().items() if v != 0}
+    if bad:
+        raise NativeError(f"in-kernel watchdog fired: {bad} (a wait for a peer CTA / TMA / MMA timed out; "
+                          "see INTEGRATION.md: B200RNN_PERSIST / B200RNN_WAVE)")
+
+
 def check(rc: int, what: str = "") -> None:
     if rc != 0:
         msg = lib().b200rnn_last_error().decode("utf-8", "replace")

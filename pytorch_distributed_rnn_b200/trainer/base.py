@@ -169,6 +169,9 @@ class Trainer:
         comm = self._get_comm()
         if comm is not None and hasattr(comm, "check"):
             comm.check()   # surface a fired comm watchdog (dead / stuck peer) instead of training on garbage
+        if cuda:
+            from .. import _native
+            _native.assert_device_healthy()   # same for the kernels' own bounded waits (TMA / MMA / wavefront)
         logging.info(formatter.performance_message(peak_rss_mib(), duration))
         if cuda:
             logging.info("Rank: {:02d}   Device time: {:.6f} s, peak device memory: {:.1f} MiB".format(
