@@ -257,6 +257,10 @@ int b200rnn_persist_status(int32_t* status);
  * consumer CTA never saw its producer's values; results of that call are then garbage).
  * B200RNN_WAVE=0 keeps the layers of a batch tile in one CTA, in sequence. */
 int b200rnn_wave_status(int32_t* status);
+/* Whether the small-hidden forward / backward of this shape is launched as a layer wavefront (each then
+ * issues one extra small kernel, the sentinel pre-fill, before the main one). */
+int b200rnn_rnn_small_fwd_wave(const b200rnn_model_desc* d);
+int b200rnn_rnn_small_bwd_wave(const b200rnn_model_desc* d);
 
 /* ---- L2 flush helper for benchmarking (writes `bytes` of scratch). */
 int b200rnn_l2_flush(void* scratch, int64_t bytes, void* stream);

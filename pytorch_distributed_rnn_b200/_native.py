@@ -90,6 +90,8 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_rnn_persist_supported": (i32, [P(ModelDesc)]),
         "b200rnn_persist_status": (i32, [P(i32)]),
         "b200rnn_wave_status": (i32, [P(i32)]),
+        "b200rnn_rnn_small_fwd_wave": (i32, [P(ModelDesc)]),
+        "b200rnn_rnn_small_bwd_wave": (i32, [P(ModelDesc)]),
         "b200rnn_lstm_bwd_dx": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp, vp]),
         "b200rnn_gru_bwd_dx": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
         "b200rnn_lstm_bwd_static": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),

@@ -86,6 +86,12 @@ class FusedTrainEngine:
         d.n_params = a.numel
         return d
 
+    def _fwd_wave(self, d: ModelDesc) -> int:
+        """1 if the forward of this shape is a layer wavefront (the tcgen05 forward never is)."""
+        if self.fwd_kind == "tc" and self.model.cell == "lstm":
+            return 0
+        return int(self.lib.b200rnn_rnn_small_fwd_wave(C.byref(d)))
+
     def _get(self, B: int, T: int) -> dict:
         key = (B, T)
         buf = self._bufs.get(key)
@@ -95,6 +101,9 @@ class FusedTrainEngine:
             _native.check(self.lib.b200rnn_rnn_small_tiling(C.byref(d), C.byref(rb), C.byref(nc)), "tiling")
             buf = dict(
                 desc=d, n_cta=nc.value, rows_per_cta=rb.value,
+                # kernels per step: forward, backward, reduce+update (+ one sentinel pre-fill per wavefront kernel)
+                fwd_launches=1 + self._fwd_wave(d),
+                step_launches=3 + self._fwd_wave(d) + int(self.lib.b200rnn_rnn_small_bwd_wave(C.byref(d))),
                 stash=torch.empty(self.lib.b200rnn_rnn_stash_floats(C.byref(d)), dtype=torch.float32, device=self.device),
                 scratch=torch.empty(self.lib.b200rnn_rnn_bwd_scratch_floats(C.byref(d)), dtype=torch.float32, device=self.device),
                 x=None, y=None)
@@ -123,7 +132,7 @@ class FusedTrainEngine:
                 opt.exp_avg_sq.data_ptr(), C.byref(o), None, slot.data_ptr(), sp), "fused_update")
         else:
             self.comm.allreduce_update(buf["scratch"], buf["n_cta"], a, opt, o, slot)
-        _native.count_launch(3)
+        _native.count_launch(buf["step_launches"])
         self.n_steps += 1
         return slot
 
@@ -231,5 +240,5 @@ class FusedTrainEngine:
         h_last = buf["stash"][((L - 1) * T + (T - 1)) * B * H:][:B * H]
         _native.check(self.lib.b200rnn_head_fwd(h_last.data_ptr(), H, m.fc.weight.data_ptr(), m.fc.bias.data_ptr(),
                                                 y.data_ptr(), B, H, m.output_dim, None, self.eval_metrics.data_ptr(), sp), "head_fwd")
-        _native.count_launch(3)
+        _native.count_launch(2 + buf["fwd_launches"])
         return self.eval_metrics[:2]
