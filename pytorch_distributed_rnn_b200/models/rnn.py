@@ -114,6 +114,33 @@ class FusedRNNBase(nn.Module):
                     getattr(self, f"bias_ih_l{l}"), getattr(self, f"bias_hh_l{l}")]
         return out
 
+    # -- nn.LSTM / nn.GRU API compatibility --
+    def flatten_parameters(self) -> None:
+        """No-op (kept so code written for ``nn.LSTM`` runs unchanged): the fused kernels read the weights in
+        place — zero-copy when a :class:`~..utils.arena.ParamArena` owns the model — instead of cuDNN's packed blob."""
+
+    @property
+    def all_weights(self) -> List[List[torch.Tensor]]:
+        """``[[weight_ih_l0, weight_hh_l0, bias_ih_l0, bias_hh_l0], ...]`` like ``nn.LSTM.all_weights``."""
+        w = self.flat_weights()
+        return [w[4 * l:4 * l + 4] for l in range(self.num_layers)]
+
+    @property
+    def bias(self) -> bool:
+        return True
+
+    @property
+    def bidirectional(self) -> bool:
+        return False
+
+    @property
+    def dropout(self) -> float:
+        return 0.0
+
+    @property
+    def proj_size(self) -> int:
+        return 0
+
     def extra_repr(self) -> str:
         return f"{self.input_size}, {self.hidden_size}, num_layers={self.num_layers}, batch_first={self.batch_first}"
 

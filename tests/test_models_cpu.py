@@ -69,3 +69,14 @@ def test_arena_views_share_memory():
     assert all(float(p.abs().sum()) == 0 for p in m.parameters())
     m(torch.randn(2, 4, 9)).sum().backward()
     assert float(a.grad[:a.numel].abs().sum()) > 0  # autograd accumulated into the arena views
+
+
+def test_rnn_modules_expose_the_stock_attribute_surface():
+    """Code written against nn.LSTM / nn.GRU (flatten_parameters, all_weights, bias, ...) runs unchanged."""
+    for cls, stock in ((FusedLSTM, nn.LSTM), (FusedGRU, nn.GRU)):
+        m, ref = cls(9, 32, 2, batch_first=True), stock(9, 32, 2, batch_first=True)
+        m.flatten_parameters()
+        assert [[tuple(t.shape) for t in layer] for layer in m.all_weights] == \
+               [[tuple(t.shape) for t in layer] for layer in ref.all_weights]
+        for attr in ("input_size", "hidden_size", "num_layers", "bias", "batch_first", "dropout", "bidirectional", "proj_size"):
+            assert getattr(m, attr) == getattr(ref, attr), attr
