@@ -33,3 +33,24 @@ def test_local_run_resume_and_periodic_checkpoint(tiny_dataset_dir, tmp_path):
     assert (tmp_path / "ck" / "best-model.pt").exists() and (tmp_path / "ck" / "checkpoint-epoch-1.pt").exists()
     t2 = cli.main([*common, "--epochs", "2", "--resume", str(tmp_path / "ck" / "checkpoint-epoch-1.pt"), "local"])
     assert t2.start_epoch == 1 and t2.optimizer.step_count == 2 * t.optimizer.step_count
+
+
+def test_gru_cell_trains_and_checkpoints_load_into_stock_gru(tiny_dataset_dir, tmp_path):
+    """`--cell gru` (an extension: the reference only builds nn.LSTM) keeps the checkpoint key names and loads
+    into a stock torch GRU + Linear."""
+    import torch
+    from torch import nn
+    t = cli.main(["--dataset-path", str(tiny_dataset_dir), "--batch-size", "96", "--seed", "7", "--device", "cpu",
+                  "--cell", "gru", "--epochs", "1", "--checkpoint-directory", str(tmp_path / "ck"),
+                  "--history-path", str(tmp_path / "h.json"), "local"])
+    assert t.model.cell == "gru"
+    ck = torch.load(tmp_path / "ck" / "best-model.pt", map_location="cpu", weights_only=False)
+    state = ck["model_state"]
+    assert set(state) == {f"lstm.{w}_l{l}" for w in ("weight_ih", "weight_hh", "bias_ih", "bias_hh") for l in range(2)} | {"fc.weight", "fc.bias"}
+    gru = nn.GRU(9, 32, 2, batch_first=True)
+    gru.load_state_dict({k[len("lstm."):]: v for k, v in state.items() if k.startswith("lstm.")})
+    x = torch.randn(4, 128, 9)
+    with torch.no_grad():
+        want = gru(x)[0][:, -1] @ state["fc.weight"].t() + state["fc.bias"]
+        got = t.model(x)
+    assert torch.allclose(got, want, atol=1e-5)
