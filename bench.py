@@ -218,6 +218,10 @@ def run_own(args):
         sampler.stop()
         clocks = sampler.summary([(t_a, t_b), (t_c, t_d)])
 
+    # a number produced while an in-kernel watchdog fired (a CTA gave up waiting for its producer) is garbage:
+    # fail loudly instead of printing it (outside every timed region)
+    _native.assert_device_healthy()
+
     if rank == 0:
         value = GLOBAL_BATCH * K / (dev_ms / 1e3)
         out = {
