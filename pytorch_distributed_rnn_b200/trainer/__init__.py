@@ -1,16 +1,18 @@
-"""Trainer family + sub-command registry + the ``train(args, trainer_cls)`` driver.
+"""Trainer family, the sub-command registry and the run driver behind the CLI.
 
-Parity: src/motion/trainer/__init__.py — sub-commands ``local`` / ``distributed`` /
-``horovod`` (:10-18); ``train`` sets the log level, loads the datasets, drops validation/test
-under ``--no-validation``, builds ``MotionModel`` and the trainer, trains, and dumps
-``history.json`` (:21-60).  Deviations: ``--validation-fraction`` is honoured
-(Q2), ``history.json`` is written by rank 0 only (Q8), the numpy split RNG follows ``--seed``
-(Q14).
+Capability parity with src/motion/trainer/__init__.py (sub-commands ``local`` / ``distributed`` /
+``horovod``, :10-18; a run = set the log level, load the three datasets, optionally drop validation and
+test, build the model and the trainer, train, write ``history.json``, :21-60).  Deviations:
+``--validation-fraction`` is honoured (Q2), only rank 0 writes ``history.json`` (Q8), the numpy split RNG
+follows ``--seed`` (Q14).  Extensions reach the trainer through optional CLI attributes (``--cell``,
+``--device``, ``--deferred-logging``, ``--save-every``, ``--resume``, ``--history-path``).
 """
 from __future__ import annotations
 
 import json
 import logging
+from functools import partial
+from typing import Dict, Type
 
 from ..data.dataset import MotionDataset
 from ..models.motion import MotionModel
@@ -21,43 +23,53 @@ from .formatter import TrainingMessageFormatter
 from .horovod import HorovodTrainer
 
 __all__ = ["Trainer", "DistributedTrainer", "DDPTrainer", "HorovodTrainer", "TrainingMessageFormatter",
-           "add_sub_commands", "train"]
+           "TRAINERS", "add_sub_commands", "train"]
+
+# sub-command -> trainer class (the parameter-server sub-command registers itself in parallel/param_server.py)
+TRAINERS: Dict[str, Type[Trainer]] = {"local": Trainer, "distributed": DDPTrainer, "horovod": HorovodTrainer}
+
+# optional CLI attributes forwarded to the trainer constructor: attribute name -> (keyword, default)
+_OPTIONAL = {"device": ("device", None), "deferred_logging": ("deferred_logging", False),
+             "save_every": ("save_every", 0), "resume": ("resume", None)}
 
 
-def add_sub_commands(sub_parser):
-    create_parser(sub_parser, "local", Trainer)
-    create_parser(sub_parser, "distributed", DDPTrainer)
-    create_parser(sub_parser, "horovod", HorovodTrainer)
+def add_sub_commands(sub_parser) -> None:
+    for name, cls in TRAINERS.items():
+        sub_parser.add_parser(name).set_defaults(func=partial(_run, trainer_cls=cls))
 
 
-def create_parser(sub_parser, name, trainer_class):
-    parser = sub_parser.add_parser(name)
-    parser.set_defaults(func=lambda args: train(args, trainer_class))
+def _run(args, trainer_cls):
+    return train(args, trainer_cls)
+
+
+def _datasets(args):
+    splits = MotionDataset.load(args.dataset_path, output_path=args.output_path,
+                                validation_fraction=args.validation_fraction, seed=args.seed)
+    names = ("Training", "Validation", "Test")
+    keep = 1 if args.no_validation else 3
+    for name, ds in list(zip(names, splits))[:keep]:
+        logging.info(f"{name} set of size {len(ds)}")
+    return tuple(ds if i < keep else None for i, ds in enumerate(splits))
+
+
+def _write_history(args, train_history, validation_history) -> None:
+    path = getattr(args, "history_path", None) or "history.json"
+    with open(path, "w") as fh:
+        json.dump({"train_history": train_history, "validation_history": validation_history}, fh)
 
 
 def train(args, trainer_cls):
+    """One CLI run: returns the trainer (tests and notebooks inspect it)."""
     logging.getLogger().setLevel(args.log)
-    training_set, validation_set, test_set = MotionDataset.load(
-        args.dataset_path, output_path=args.output_path,
-        validation_fraction=args.validation_fraction, seed=args.seed)
-    logging.info(f"Training set of size {len(training_set)}")
-    if args.no_validation:
-        validation_set = None
-        test_set = None
-    else:
-        logging.info(f"Validation set of size {len(validation_set)}")
-        logging.info(f"Test set of size {len(test_set)}")
-    model = MotionModel(input_dim=training_set.num_features, hidden_dim=args.hidden_units,
-                        layer_dim=args.stacked_layer, output_dim=len(MotionDataset.LABELS),
-                        cell=getattr(args, "cell", "lstm"))
-    trainer = trainer_cls(
-        model=model, training_set=training_set, validation_set=validation_set, test_set=test_set,
-        batch_size=args.batch_size, learning_rate=args.learning_rate, checkpoint_dir=args.checkpoint_directory,
-        device=getattr(args, "device", None), deferred_logging=getattr(args, "deferred_logging", False),
-        save_every=getattr(args, "save_every", 0), resume=getattr(args, "resume", None))
+    train_ds, val_ds, test_ds = _datasets(args)
+    net = MotionModel(train_ds.num_features, args.hidden_units, args.stacked_layer, len(MotionDataset.LABELS),
+                      cell=getattr(args, "cell", "lstm"))
+    extras = {kw: getattr(args, attr, default) for attr, (kw, default) in _OPTIONAL.items()}
+    trainer = trainer_cls(model=net, training_set=train_ds, validation_set=val_ds, test_set=test_ds,
+                          batch_size=args.batch_size, learning_rate=args.learning_rate,
+                          checkpoint_dir=args.checkpoint_directory, **extras)
     logging.info(f"Training model for {args.epochs} epochs...")
     _, train_history, validation_history = trainer.train(epochs=args.epochs)
     if getattr(trainer, "rank", 0) == 0:
-        with open(getattr(args, "history_path", None) or "history.json", "w") as file:
-            json.dump({"train_history": train_history, "validation_history": validation_history}, file)
+        _write_history(args, train_history, validation_history)
     return trainer
