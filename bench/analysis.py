@@ -18,7 +18,12 @@ import re
 import statistics
 from collections import defaultdict
 
-PERF_RE = re.compile(r"(\d+): Memory Usage: (\d+\.\d+), Training Duration: (\d+\.\d+)")
+import sys
+from pathlib import Path
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from pytorch_distributed_rnn_b200.trainer.formatter import parse_log  # noqa: E402  (the log-line contract's parsers)
+
 SIZE_RE = re.compile(r"Training set of size (\d+)")
 
 
@@ -30,7 +35,7 @@ def load(files):
                 if r["command"] in seen:
                     continue
                 seen.add(r["command"])
-                perf = PERF_RE.findall(r.get("stderr", ""))
+                perf = [rec for rec in parse_log(r.get("stderr", "")) if rec["kind"] == "performance"]
                 if not perf:
                     continue
                 m = SIZE_RE.search(r.get("stderr", ""))
@@ -38,8 +43,8 @@ def load(files):
                 params = cfg.get("parameters", {})
                 rows.append({
                     "trainer": cfg.get("trainer", r.get("trainer")), "ranks": cfg.get("hosts", 0) * cfg.get("slots", 1) or None,
-                    "batch": params.get("--batch-size", 1440), "seconds": max(float(p[2]) for p in perf),
-                    "memory": max(float(p[1]) for p in perf), "samples": int(m.group(1)) if m else 6912,
+                    "batch": params.get("--batch-size", 1440), "seconds": max(p["duration"] for p in perf),
+                    "memory": max(p["memory"] for p in perf), "samples": int(m.group(1)) if m else 6912,
                     "rule_type": r.get("rule_type"), "rule_value": r.get("rule_value")})
     return rows
 

@@ -11,44 +11,28 @@ import sys
 
 import numpy as np
 import torch
-from torch import nn, optim
-from torch.utils.data import DataLoader
+from torch import optim
 
-import _path  # noqa: F401
-from pytorch_distributed_rnn_b200 import ToyDataset, ToyModel, params_checksum
+import _toy
+from pytorch_distributed_rnn_b200 import ToyModel, params_checksum
 from pytorch_distributed_rnn_b200.data.sampler import ShardedEpochSampler
 from pytorch_distributed_rnn_b200.parallel import process_group as pg
 from pytorch_distributed_rnn_b200.parallel.ddp import DistributedDataParallel as DDP
 
 
 def run(rank, world_size, device, sharded=False, quiet=False):
-    say = (lambda *a: None) if quiet else print
+    say = _toy.reporter(rank, quiet)
     torch.manual_seed(0)
     np.random.seed(0)
-    model = ToyModel().to(device)
-    say("rank", rank, "initial:", params_checksum(model))
-    ddp_model = DDP(model)
-    say("rank", rank, "synced:", params_checksum(ddp_model))
-    loss_fn = nn.MSELoss()
-    optimizer = optim.SGD(ddp_model.parameters(), lr=0.001)
-    optimizer.zero_grad()
-    dataset = ToyDataset(size=24)
-    batch_size = 12 // world_size
-    sampler = ShardedEpochSampler(len(dataset), world_size, rank, shuffle=False) if sharded else None
-    loader = DataLoader(dataset=dataset, batch_size=batch_size, sampler=sampler)
-    for inputs, labels in loader:
-        inputs, labels = inputs.to(device), labels.to(device)
-        optimizer.zero_grad()
-        outputs = ddp_model(inputs)
-        say("rank", rank, "batch:", float(inputs.sum() + labels.sum()))
-        loss = loss_fn(outputs, labels)
-        say("rank", rank, "loss:", loss.item())
-        loss.backward()
-        optimizer.step()
-        say("rank", rank, "parameters:", params_checksum(ddp_model))
-        g = optimizer.param_groups[0]["params"][0].grad
-        say("rank", rank, "grad:", float(g.sum()) if g is not None else None)
-    return ddp_model
+    net = ToyModel().to(device)
+    say("initial", params_checksum(net))
+    replica = DDP(net)     # broadcasts rank 0's parameters; averages gradients bucket by bucket during backward
+    say("synced", params_checksum(replica))
+    sgd = optim.SGD(replica.parameters(), lr=_toy.LR)
+    shard = ShardedEpochSampler(24, world_size, rank, shuffle=False) if sharded else None
+    _toy.training_pass(replica, sgd, _toy.toy_loader(world_size, sampler=shard), device, say,
+                       grad_of=sgd.param_groups[0]["params"][0])
+    return replica
 
 
 if __name__ == "__main__":

@@ -1,70 +1,85 @@
-"""In-memory motion dataset + ``.pt`` cache (parity with src/motion/dataset.py).
+"""In-memory motion dataset and its on-disk tensor cache.
 
-``MotionDataset.load(base_path, output_path, validation_fraction)`` looks for
-``X_{train,validation,test}.pt`` / ``y_*.pt`` under ``base_path`` (dataset.py:38-51,71-73);
-if all six exist they are ``torch.load``-ed, otherwise the raw UCI-HAR text files are
-preprocessed and the six tensors are written to ``output_path or base_path``.  The cache
-files are plain ``torch.save`` tensors, interchangeable with the reference's.
+Capability parity with src/motion/dataset.py: ``MotionDataset.load(base_path, output_path, validation_fraction)``
+returns the (train, validation, test) datasets, from the six cached tensors ``X_<split>.pt`` / ``y_<split>.pt``
+under ``base_path`` when all of them exist (dataset.py:38-51,71-73), otherwise by preprocessing the raw UCI-HAR
+text files and writing the cache to ``output_path or base_path``.  The cache files are plain ``torch.save``
+tensors, interchangeable with the reference's.
 
-``to(device)`` makes the dataset device-resident so batches are formed by the K11 gather
-kernel instead of a host DataLoader.
+Beyond the reference: ``to(device)`` makes a dataset device-resident, so training batches are formed by the K11
+gather kernel from an index vector instead of by a host DataLoader; ``seed`` makes the validation split
+reproducible (quirk Q14).
 """
 from __future__ import annotations
 
 import logging
 from pathlib import Path
-from typing import Optional
+from typing import Dict, Optional, Tuple
 
 import torch
 from torch.utils import data
 
 from .processor import MotionDataProcessor
 
+SPLITS = ("train", "validation", "test")
+
+
+class _TensorCache:
+    """The six ``.pt`` files of one dataset directory."""
+
+    def __init__(self, directory):
+        self.directory = Path(directory)
+
+    def paths(self, split: str) -> Tuple[Path, Path]:
+        return self.directory / f"X_{split}.pt", self.directory / f"y_{split}.pt"
+
+    def complete(self) -> bool:
+        return all(p.exists() for split in SPLITS for p in self.paths(split))
+
+    def read(self) -> Dict[str, Tuple[torch.Tensor, torch.Tensor]]:
+        return {split: tuple(torch.load(p) for p in self.paths(split)) for split in SPLITS}
+
+    def write(self, tensors: Dict[str, Tuple[torch.Tensor, torch.Tensor]]) -> None:
+        self.directory.mkdir(parents=True, exist_ok=True)
+        for split, pair in tensors.items():
+            for path, tensor in zip(self.paths(split), pair):
+                torch.save(tensor, path)
+
 
 class MotionDataset(data.Dataset):
     LABELS = ["WALKING", "WALKING_UPSTAIRS", "WALKING_DOWNSTAIRS", "SITTING", "STANDING", "LAYING"]
 
     def __init__(self, features: torch.Tensor, labels: torch.Tensor):
-        self.features = features
-        self.labels = labels
-        self.seq_length = self.features.shape[1]
-        self.num_features = self.features.shape[2]
+        assert len(features) == len(labels), "features and labels differ in length"
+        self.features, self.labels = features, labels
+        _, self.seq_length, self.num_features = features.shape
+
+    def __len__(self) -> int:
+        return self.features.shape[0]
 
     def __getitem__(self, index):
         return self.features[index], self.labels[index]
 
-    def __len__(self):
-        return len(self.features)
-
     def to(self, device, pin: bool = False) -> "MotionDataset":
-        f = self.features.contiguous().float()
-        l = self.labels.contiguous().long()
-        if pin and torch.cuda.is_available() and not f.is_cuda:
-            f, l = f.pin_memory(), l.pin_memory()
-        return MotionDataset(f.to(device, non_blocking=True), l.to(device, non_blocking=True))
+        """A copy resident on ``device`` (fp32 features, int64 labels, contiguous: what the gather kernel reads)."""
+        feats, labels = self.features.contiguous().float(), self.labels.contiguous().long()
+        if pin and torch.cuda.is_available() and not feats.is_cuda:
+            feats, labels = feats.pin_memory(), labels.pin_memory()
+        return MotionDataset(feats.to(device, non_blocking=True), labels.to(device, non_blocking=True))
+
+    @classmethod
+    def get_data_path(cls, base_path, data_type: str) -> Tuple[Path, Path]:
+        return _TensorCache(base_path).paths(data_type)
 
     @classmethod
     def load(cls, base_path, output_path=None, validation_fraction: float = 0.05, seed: Optional[int] = None):
-        base_path = Path(base_path)
-        types = ["train", "validation", "test"]
-        datasets = []
-        for t in types:
-            fp, lp = cls.get_data_path(base_path, t)
-            if fp.exists() and lp.exists():
-                datasets.append(cls(torch.load(fp), torch.load(lp)))
-        if len(datasets) == 3:
+        cache = _TensorCache(base_path)
+        if cache.complete():
             logging.info("Preprocessed data found. Skip preprocessing.")
-            return datasets
-        output_path = base_path if output_path is None else Path(output_path)
-        logging.info("No processed data found. Preprocess raw data...")
-        (xtr, ytr), (xv, yv), (xte, yte) = MotionDataProcessor(seed).process_data(base_path, validation_fraction)
-        output_path.mkdir(parents=True, exist_ok=True)
-        for name, t in (("X_train", xtr), ("y_train", ytr), ("X_validation", xv), ("y_validation", yv),
-                        ("X_test", xte), ("y_test", yte)):
-            torch.save(t, output_path / f"{name}.pt")
-        return cls(xtr, ytr), cls(xv, yv), cls(xte, yte)
-
-    @classmethod
-    def get_data_path(cls, base_path, data_type):
-        base_path = Path(base_path)
-        return base_path / f"X_{data_type}.pt", base_path / f"y_{data_type}.pt"
+            tensors = cache.read()
+        else:
+            logging.info("No processed data found. Preprocess raw data...")
+            parts = MotionDataProcessor(seed).process_data(Path(base_path), validation_fraction)
+            tensors = dict(zip(SPLITS, parts))
+            _TensorCache(base_path if output_path is None else output_path).write(tensors)
+        return tuple(cls(*tensors[split]) for split in SPLITS)

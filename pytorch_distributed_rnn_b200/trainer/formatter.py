@@ -8,7 +8,8 @@ src/motion/trainer/formatter.py:6-27.
 """
 from __future__ import annotations
 
-from typing import Optional
+import re
+from typing import Dict, Iterator, Optional
 
 
 def percentage(current, overall) -> float:
@@ -43,3 +44,44 @@ class TrainingMessageFormatter:
 
     def performance_message(self, memory, duration) -> str:
         return f"{self.rank}: Memory Usage: {memory}, Training Duration: {duration}"
+
+
+# ---------------------------------------------------------------------------
+# The inverse direction: parsers for the lines above.  The reference only ever parses the performance line
+# (one regex inside a notebook); here every message has a parser, so logs of either implementation can be
+# turned back into numbers (bench/analysis.py, tests/test_formatter.py round-trips) without copying regexes.
+# ---------------------------------------------------------------------------
+_RANK = r"Rank: (?P<rank>\d+)   "
+PATTERNS: Dict[str, "re.Pattern[str]"] = {
+    "epoch_start": re.compile(_RANK + r"Start Epoch (?P<epoch>\d+)"),
+    "train_progress": re.compile(
+        _RANK + r"Train Batch: (?P<batch>\d+)/(?P<batches>\d+) \((?P<pct>\d+)%\)\tLoss: (?P<loss>-?[\d.]+(?:e-?\d+)?|nan|inf)"
+        r"\tAcc: (?P<correct>\d+)/(?P<examples>\d+) \((?P<acc_pct>\d+)%\)"),
+    "evaluation": re.compile(
+        r"(?:Test Evaluation:|Evaluation Epoch: (?P<epoch>\d+)/(?P<epochs>\d+) \((?P<pct>\d+)%\))\t"
+        r"Loss: (?P<loss>-?[\d.]+|nan|inf)\t Accuracy: (?P<correct>\d+)/(?P<examples>\d+) \((?P<acc_pct>\d+)%\)"),
+    "performance": re.compile(r"(?P<rank>\d+): Memory Usage: (?P<memory>\d+\.\d+), Training Duration: (?P<duration>\d+\.\d+)"),
+}
+_INT = {"rank", "epoch", "epochs", "batch", "batches", "pct", "correct", "examples", "acc_pct"}
+
+
+def parse_line(line: str) -> Optional[dict]:
+    """Return ``{"kind": ..., <fields as int / float>}`` for a trainer log line, or None if it is something else."""
+    for kind, pat in PATTERNS.items():
+        m = pat.search(line)
+        if m is None:
+            continue
+        out = {"kind": kind}
+        for k, v in m.groupdict().items():
+            if v is not None:
+                out[k] = int(v) if k in _INT else float(v)
+        return out
+    return None
+
+
+def parse_log(text: str) -> Iterator[dict]:
+    """All recognised trainer lines of a captured stdout / stderr, in order."""
+    for line in text.splitlines():
+        rec = parse_line(line)
+        if rec is not None:
+            yield rec
