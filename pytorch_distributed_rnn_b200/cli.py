@@ -22,64 +22,78 @@ DEFAULT_CHECKPOINT_DIR = PKG_DIR / "models_ckpt"
 DEFAULT_DATASET_PATH = PKG_DIR / "data_cache"
 
 
+# The reference's global flags (name, default, type) — an interface: recorded experiment commands must replay.
+REFERENCE_FLAGS = (
+    ("checkpoint-directory", DEFAULT_CHECKPOINT_DIR, Path),
+    ("dataset-path", DEFAULT_DATASET_PATH, Path),
+    ("output-path", None, Path),
+    ("stacked-layer", 2, int),
+    ("hidden-units", 32, int),
+    ("epochs", 100, int),
+    ("validation-fraction", 0.1, float),
+    ("batch-size", 1440, int),
+    ("learning-rate", 0.0025, float),
+    ("dropout", 0.1, float),          # parsed, unused (quirk Q1)
+    ("log", "INFO", str),
+    ("num-threads", 4, int),          # parsed, unused (quirk Q3)
+    ("seed", None, int),
+)
+# Extensions (name, argparse keyword arguments)
+EXTENSION_FLAGS = (
+    ("cell", dict(default="lstm", choices=["lstm", "gru"])),
+    ("device", dict(default=None, help="cpu | cuda | cuda:N (default: this rank's GPU if any)")),
+    ("deferred-logging", dict(action="store_true",
+                              help="render per-batch lines once per epoch from the device ring buffer (no per-step host sync)")),
+    ("save-every", dict(default=0, type=int, help="also write checkpoint-epoch-N.pt every N epochs")),
+    ("resume", dict(default=None, type=Path, help="checkpoint to resume from")),
+    ("history-path", dict(default=None, type=Path)),
+    ("synthetic", dict(action="store_true",
+                       help="write a synthetic dataset of the reference's shape to --dataset-path if none is there")),
+)
+
+
 def build_parser() -> argparse.ArgumentParser:
     from . import trainer
     from .parallel import param_server
 
     parser = argparse.ArgumentParser(prog="pytorch_distributed_rnn_b200", description="B200-native distributed RNN training")
-    parser.add_argument("--checkpoint-directory", default=DEFAULT_CHECKPOINT_DIR, type=Path)
-    parser.add_argument("--dataset-path", default=DEFAULT_DATASET_PATH, type=Path)
-    parser.add_argument("--output-path", default=None, type=Path)
-    parser.add_argument("--stacked-layer", default=2, type=int)
-    parser.add_argument("--hidden-units", default=32, type=int)
-    parser.add_argument("--epochs", default=100, type=int)
-    parser.add_argument("--validation-fraction", default=0.1, type=float)
-    parser.add_argument("--batch-size", default=1440, type=int)
-    parser.add_argument("--learning-rate", default=0.0025, type=float)
-    parser.add_argument("--dropout", default=0.1, type=float)
-    parser.add_argument("--log", default="INFO")
-    parser.add_argument("--num-threads", default=4, type=int)
-    parser.add_argument("--seed", default=None, type=int)
+    for name, default, kind in REFERENCE_FLAGS:
+        parser.add_argument(f"--{name}", default=default, type=kind)
     parser.add_argument("--no-validation", action="store_true")
-    # extensions
-    parser.add_argument("--cell", default="lstm", choices=["lstm", "gru"])
-    parser.add_argument("--device", default=None, help="cpu | cuda | cuda:N (default: this rank's GPU if any)")
-    parser.add_argument("--deferred-logging", action="store_true",
-                        help="render per-batch lines once per epoch from the device ring buffer (no per-step host sync)")
-    parser.add_argument("--save-every", default=0, type=int, help="also write checkpoint-epoch-N.pt every N epochs")
-    parser.add_argument("--resume", default=None, type=Path, help="checkpoint to resume from")
-    parser.add_argument("--history-path", default=None, type=Path)
-    parser.add_argument("--synthetic", action="store_true",
-                        help="write a synthetic dataset of the reference's shape to --dataset-path if none is there")
-
-    sub_parser = parser.add_subparsers(title="Available commands", metavar="command [options ...]")
-    sub_parser.required = True
-    param_server.add_sub_command(sub_parser)
-    trainer.add_sub_commands(sub_parser)
+    for name, kwargs in EXTENSION_FLAGS:
+        parser.add_argument(f"--{name}", **kwargs)
+    commands = parser.add_subparsers(title="Available commands", metavar="command [options ...]")
+    commands.required = True
+    param_server.add_sub_command(commands)
+    trainer.add_sub_commands(commands)
     return parser
 
 
+def _ensure_synthetic_dataset(args) -> None:
+    """``--synthetic``: rank 0 writes the dataset if it is missing, the other ranks wait for the last file."""
+    from .data import synthetic
+    from .data.dataset import MotionDataset
+    from .parallel.process_group import env_rank_info
+    first, _ = MotionDataset.get_data_path(args.dataset_path, "train")
+    if first.exists():
+        return
+    rank, world, _ = env_rank_info()
+    if rank == 0:
+        synthetic.write_dataset(args.dataset_path, seed=args.seed or 0)
+    elif world > 1:
+        import time
+        last, _ = MotionDataset.get_data_path(args.dataset_path, "test")
+        deadline = time.monotonic() + 60.0
+        while not last.exists() and time.monotonic() < deadline:
+            time.sleep(0.1)
+
+
 def main(argv=None):
-    parser = build_parser()
-    args = parser.parse_args(argv)
+    args = build_parser().parse_args(argv)
     if args.seed is not None:
         torch.manual_seed(args.seed)
     if args.synthetic:
-        from .data import synthetic
-        from .data.dataset import MotionDataset
-        fp, _ = MotionDataset.get_data_path(args.dataset_path, "train")
-        if not fp.exists():
-            from .parallel.process_group import env_rank_info
-            rank, world, _ = env_rank_info()
-            if rank == 0:
-                synthetic.write_dataset(args.dataset_path, seed=args.seed or 0)
-            elif world > 1:
-                import time
-                tp, _ = MotionDataset.get_data_path(args.dataset_path, "test")
-                for _ in range(600):
-                    if tp.exists():
-                        break
-                    time.sleep(0.1)
+        _ensure_synthetic_dataset(args)
     return args.func(args)
 
 
