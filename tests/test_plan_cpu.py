@@ -52,3 +52,31 @@ def test_single_layer_and_deep_stacks_never_wave_in_backward():
 def test_gru_uses_the_same_plan():
     assert _plan(180, cell="gru") == {**_plan(180, cell="lstm"), "n_params": _plan(180, cell="gru")["n_params"],
                                       "scratch": _plan(180, cell="gru")["scratch"]}
+
+
+# ---- reducer bucket plan: native (csrc/runtime/reducer.cpp) vs the Python planner, arbitrary parameter lists ----
+from hypothesis import given, settings, strategies as st  # noqa: E402
+
+
+@settings(max_examples=80, deadline=None)
+@given(sizes=st.lists(st.integers(1, 3_000_000), min_size=1, max_size=40),
+       first_kb=st.integers(1, 2048), cap_kb=st.integers(1, 32768))
+def test_bucket_plan_native_equals_python_and_respects_caps(sizes, first_kb, cap_kb):
+    from pytorch_distributed_rnn_b200.parallel.ddp import plan_buckets
+    lib = _native.lib()
+    nbytes = [4 * s for s in sizes]
+    first, cap = first_kb << 10, cap_kb << 10
+    arr = (C.c_int64 * len(nbytes))(*nbytes)
+    out = (C.c_int32 * len(nbytes))()
+    nb = C.c_int32()
+    assert lib.b200rnn_bucket_plan(arr, len(nbytes), first, cap, out, C.byref(nb)) == 0
+    py = plan_buckets(nbytes, first, cap)
+    assert nb.value == len(py)
+    for b, ids in enumerate(py):
+        assert all(out[i] == b for i in ids)
+        # a bucket only exceeds its cap when a single parameter does
+        limit = first if b == 0 else cap
+        assert sum(nbytes[i] for i in ids) <= limit or len(ids) == 1
+    # reverse parameter order, every parameter exactly once
+    flat = [i for ids in py for i in ids]
+    assert flat == list(reversed(range(len(nbytes))))
