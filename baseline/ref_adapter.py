@@ -30,9 +30,12 @@ REF_MOTION = REF_ROOT / "motion"
 
 
 def unavailable_reason():
-    if not (REF_MOTION / "trainer" / "base.py").exists():
-        return ("reference not installed under baseline/_ref (run baseline/install_reference.sh; "
-                "upstream has no setup.py/pyproject so a packaging shim is needed)")
+    """None when the reference is importable; installs it first if baseline/_ref is missing."""
+    from baseline import ensure_reference
+    try:
+        ensure_reference()
+    except Exception as e:  # noqa: BLE001
+        return f"reference not installable under baseline/_ref: {type(e).__name__}: {str(e)[:300]}"
     return None
 
 
