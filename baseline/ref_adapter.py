@@ -85,6 +85,20 @@ class _DeviceLoader:
             epoch += 1
 
 
+class _EpochLoader:
+    """The reference's own DataLoader, every batch (incl. the partial last one) moved to the GPU."""
+
+    def __init__(self, loader, device):
+        self.loader, self.device, self.dataset = loader, device, loader.dataset
+
+    def __len__(self):
+        return len(self.loader)
+
+    def __iter__(self):
+        for data, labels in self.loader:
+            yield data.to(self.device), labels.to(self.device)
+
+
 def run(n_gpus, steps, warmup, rank, world, device, cfg):
     import torch
     _install_stubs()
@@ -142,6 +156,23 @@ def run(n_gpus, steps, warmup, rank, world, device, cfg):
         torch.distributed.barrier()
     wall = time.perf_counter() - t0
     t_b = time.time()
-    return {"device_s": e0.elapsed_time(e1) / 1e3, "wall_s": wall, "window": (t_a, t_b), "path": path,
+    # one epoch through the reference's own Trainer.train(1) (trainer/base.py:65-101): the BASELINE.md metric
+    trainer.train_loader = _EpochLoader(base_loader, device)
+    ep = []
+    for _ in range(2):
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize(device)
+        te = time.perf_counter()
+        trainer.train(1)
+        torch.cuda.synchronize(device)
+        ep.append(time.perf_counter() - te)
+    if world > 1:
+        t = torch.tensor(ep, dtype=torch.float64, device=device)
+        torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+        ep = [float(v) for v in t.tolist()]
+    epoch = {"first_epoch_s": ep[0], "epoch_s": ep[1], "samples": n, "steps": len(base_loader),
+             "samples_per_s": n / ep[1], "api": "reference Trainer.train(1), wall clock, max over ranks"}
+    return {"epoch": epoch,"device_s": e0.elapsed_time(e1) / 1e3, "wall_s": wall, "window": (t_a, t_b), "path": path,
             "h2d_bytes_per_step": counter["h2d"] * world, "d2h_bytes_per_step": 8 * world,
             "final_loss": None}

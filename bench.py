@@ -13,11 +13,17 @@ Rank 0 prints ONE JSON line.  Two measurements per run:
 
 * ``value``   — device time: every step bracketed by CUDA events on the launching stream, a
   256 MiB L2 flush between steps (outside the brackets), summed over K steps, max over ranks.
-  The step is K11 gather from the device-resident dataset -> fused forward -> fused
-  head/CE/backward -> fused grad-reduce/all-reduce/Adam: 4 launches of this repo's kernels.
+  The step is fused forward -> fused head/CE/backward -> fused grad-reduce/all-reduce/Adam,
+  3 launches of this repo's kernels; the batch is read from the device-resident dataset through
+  the sampler's index slice by the kernels' own loaders.
 * ``e2e``     — wall clock through the public API a user calls
-  (``FusedTrainEngine.train_steps_host``): every step copies that step's inputs from pinned
-  host memory to the GPU and reads the step's loss back to the host (copies pipelined with compute).
+  (``FusedTrainEngine.train_steps_host``): every step assembles its batch on the host from the
+  dataset and the sampler's indices (index_select into pinned memory — what the reference's
+  DataLoader does with __getitem__ + collate), copies it to the GPU and reads the step's loss back
+  to the host (assembly and copies pipelined with compute).
+* ``epoch``   — the BASELINE.md metric itself: wall clock of ONE epoch (6 912 samples: 4 full
+  batches + the partial one) through ``Trainer.train(1)`` (src/motion/trainer/base.py:93-96), cold
+  (first call, includes buffer allocation) and warm (second call); max over ranks.
 
 ``--impl reference`` runs the UNMODIFIED reference (installed at baseline/_ref) through its own
 Trainer loop on the same GPUs (stock torch cuDNN LSTM + NCCL DistributedDataParallel); see
@@ -192,26 +198,39 @@ def run_own(args):
     last = engine.metrics[(engine.n_steps - 1) % engine.METRIC_RING].cpu()
 
     # ---------------- end-to-end through the public API ----------------
-    ring = 8
-    host = []
-    for s in range(ring):
-        i = step_indices(s)
-        host.append((x_all[i].contiguous().pin_memory(), y_all[i].contiguous().view(-1).pin_memory()))
-    for _ in engine.train_steps_host(host[s % ring] for s in range(max(W, 3))):
+    # Every step's batch is ASSEMBLED on the host inside the timed region (rows of the dataset selected by the
+    # sampler's indices into pinned staging memory), then copied to the device; its loss is read back.
+    ring = 4   # pinned staging buffers: the pipeline keeps at most two copies in flight
+    y_flat = y_all.view(-1)
+    pin_x = [torch.empty(per_rank, SEQ_LEN, FEATURES).pin_memory() for _ in range(ring)]
+    pin_y = [torch.empty(per_rank, dtype=torch.int64).pin_memory() for _ in range(ring)]
+    idx_host = [step_indices(s) for s in range(max(W, 3) + K)]
+
+    def host_batches(first, count):
+        for s in range(first, first + count):
+            k = s % ring
+            torch.index_select(x_all, 0, idx_host[s], out=pin_x[k])
+            torch.index_select(y_flat, 0, idx_host[s], out=pin_y[k])
+            yield pin_x[k], pin_y[k]
+
+    for _ in engine.train_steps_host(host_batches(0, max(W, 3))):
         pass
     barrier_sync(world, dev)
     t_c = time.time()
     t0 = time.perf_counter()
     n_results = 0
-    for loss, correct in engine.train_steps_host(host[s % ring] for s in range(K)):
+    for loss, correct in engine.train_steps_host(host_batches(max(W, 3), K)):
         n_results += 1
     assert n_results == K
     barrier_sync(world, dev)
     e2e_s = time.perf_counter() - t0
     t_d = time.time()
     e2e_s = max_over_ranks(e2e_s, world, dev)
-    h2d = world * (host[0][0].numel() * 4 + host[0][1].numel() * 8)
+    h2d = world * (pin_x[0].numel() * 4 + pin_y[0].numel() * 8)
     d2h = world * 8
+
+    # ---------------- one epoch through the trainer (the BASELINE.md metric) ----------------
+    epoch = run_own_epoch(world, rank, dev, comm, x_all, y_all)
 
     clocks = None
     if sampler:
@@ -238,8 +257,10 @@ def run_own(args):
             "e2e": {"value": GLOBAL_BATCH * K / e2e_s, "unit": "samples/s", "ms_per_step": 1e3 * e2e_s / K,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "api": "FusedTrainEngine.train_steps_host(host_batches) -> yields (loss, correct) per step",
-                    "inputs": f"{ring} pre-collated pinned host batches; every step: H2D copy of its batch (side stream, "
-                              "overlapping the previous step) + D2H read of its loss (one-step lag)"},
+                    "inputs": "every step, inside the timed region: host-side batch assembly (index_select of the dataset "
+                              "rows picked by the sampler into pinned memory), H2D copy of that batch (side stream, "
+                              "overlapping the previous step) and D2H read of its loss (one-step lag)"},
+            "epoch": epoch,
             "gpu_launches": launches,
             "launches_per_step": launches / K,
             "clocks": clocks,
@@ -250,6 +271,36 @@ def run_own(args):
         import torch.distributed as dist
         barrier_sync(world, dev)
         dist.destroy_process_group()
+
+
+def run_own_epoch(world, rank, dev, comm, x_all, y_all):
+    """Wall clock of one epoch (5 steps incl. the partial 1 152-sample batch) through Trainer.train(1): the public
+    training entry point, dataset device-resident (uploaded by the trainer's constructor, outside the clock — the
+    reference loads its dataset before the clock starts too, trainer/__init__.py:24-27 vs base.py:93)."""
+    import logging
+    import torch
+    from pytorch_distributed_rnn_b200 import MotionModel
+    from pytorch_distributed_rnn_b200.data.dataset import MotionDataset
+    from pytorch_distributed_rnn_b200.trainer.base import Trainer
+    logging.getLogger().setLevel("WARNING")
+    torch.manual_seed(SEED)
+    model = MotionModel(FEATURES, HIDDEN, LAYERS, CLASSES)
+    train = MotionDataset(x_all, y_all)
+    if world > 1:
+        from pytorch_distributed_rnn_b200.trainer.ddp import DDPTrainer
+        trainer = DDPTrainer(model, train, GLOBAL_BATCH, LR, device=dev, comm=comm)
+    else:
+        trainer = Trainer(model, train, GLOBAL_BATCH, LR, device=dev)
+    times = []
+    for _ in range(2):
+        barrier_sync(world, dev)
+        t0 = time.perf_counter()
+        trainer.train(1)
+        torch.cuda.synchronize(dev)
+        times.append(max_over_ranks(time.perf_counter() - t0, world, dev))
+    return {"first_epoch_s": times[0], "epoch_s": times[1], "samples": TRAIN_SIZE, "steps": 5,
+            "samples_per_s": TRAIN_SIZE / times[1],
+            "api": "Trainer.train(1) / DDPTrainer.train(1), wall clock, max over ranks"}
 
 
 def run_reference(args):
@@ -291,6 +342,7 @@ def run_reference(args):
                        "timing": "CUDA events around the reference's own _train_step loop (K steps), max over ranks"},
             "e2e": {"value": GLOBAL_BATCH * K / wall_s, "unit": "samples/s", "ms_per_step": 1e3 * wall_s / K,
                     "h2d_bytes_per_step": res["h2d_bytes_per_step"], "d2h_bytes_per_step": res["d2h_bytes_per_step"]},
+            "epoch": res.get("epoch"),
             "gpu_launches": None,
             "clocks": clocks,
             "final_loss": res.get("final_loss"),

@@ -17,6 +17,8 @@
 // results everywhere (the reference's "equal final parameters" criterion, README.md:9).
 #include "../common.cuh"
 #include "../optim.cuh"
+#include "../rows.cuh"
+#include <cstdlib>
 
 namespace b200rnn {
 namespace {
@@ -24,20 +26,37 @@ namespace {
 constexpr int kThreads = 256;
 constexpr int kElems = 4;                       // elements per thread in the two-shot kernel
 constexpr int kBlockElems = kThreads * kElems;  // 1024 parameters per two-shot block
-constexpr long long kDefaultTimeout = 4000000000LL;  // ~2 s of SM clocks
+// Watchdog of every in-kernel wait, in SM clocks (~2 GHz).  Ranks may legitimately be seconds apart (rank 0
+// validating / checkpointing while the others already wait in the next step's all-reduce, a first-step lazy
+// module load), so the default is generous: 60 s.  B200RNN_COMM_TIMEOUT_MS overrides it for the process,
+// ctx->timeout_cycles per communicator.  A wait that does time out sets a status bit (b200rnn_comm_status);
+// the values computed by that call are garbage and the trainers abort at the next check.
+constexpr long long kDefaultTimeout = 120000000000LL;
+long long default_timeout_cycles() {
+  static const long long v = [] {
+    const char* e = std::getenv("B200RNN_COMM_TIMEOUT_MS");
+    if (e != nullptr && e[0] != 0) {
+      const long long ms = std::atoll(e);
+      if (ms > 0) return ms * 2000000LL;
+    }
+    return kDefaultTimeout;
+  }();
+  return v;
+}
 
 struct Ctx {  // device-side view
   int rank, world, max_blocks, delay_ns;
-  long long inbox_floats, timeout;
+  long long inbox_floats, timeout, ll_floats;
   char* base[B200RNN_MAX_PEERS];
-  long long off_flags_ar, off_flags_pr, off_flags_sig, off_flags_bar, off_status, off_inbox, off_heap;
+  long long off_flags_ar, off_flags_pr, off_flags_sig, off_flags_bar, off_status, off_inbox, off_heap, off_ll;
 };
 
 Ctx to_dev(const b200rnn_comm_ctx* c) {
   Ctx d;
   d.rank = c->rank; d.world = c->world; d.max_blocks = c->max_blocks; d.delay_ns = c->delay_ns;
   d.inbox_floats = c->inbox_floats;
-  d.timeout = c->timeout_cycles > 0 ? c->timeout_cycles : kDefaultTimeout;
+  d.timeout = c->timeout_cycles > 0 ? c->timeout_cycles : default_timeout_cycles();
+  d.ll_floats = c->ll_floats; d.off_ll = c->off_ll;
   for (int i = 0; i < B200RNN_MAX_PEERS; ++i) d.base[i] = (char*)c->base[i];
   d.off_flags_ar = c->off_flags_ar; d.off_flags_pr = c->off_flags_pr; d.off_flags_sig = c->off_flags_sig;
   d.off_flags_bar = c->off_flags_bar; d.off_status = c->off_status; d.off_inbox = c->off_inbox;
@@ -47,6 +66,9 @@ Ctx to_dev(const b200rnn_comm_ctx* c) {
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
@@ -125,43 +147,45 @@ __device__ __forceinline__ F4 load4_cg(const float* src, long long i, long long 
 // Block b handles elements [b*1024, (b+1)*1024) (4 per thread, 128-bit peer stores); flags are per
 // (source, block), so blocks are independent and no grid-wide synchronisation exists.
 // ---------------------------------------------------------------------------
-template <bool UPDATE, int ELEMS>
+template <bool UPDATE>
 __global__ void __launch_bounds__(kThreads) oneshot_kernel(
-    Ctx c, uint32_t seq, const float* __restrict__ rows, int n_rows, long long n, long long row_stride,
+    Ctx c, uint32_t seq, const float* __restrict__ rows, long long n, long long row_stride,
     float* buf /* UPDATE: params, else in/out vector */, float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
     OptScalars o, float scale, float* __restrict__ metrics) {
-  const long long i = ((long long)blockIdx.x * kThreads + threadIdx.x) * ELEMS;
+  const long long i = ((long long)blockIdx.x * kThreads + threadIdx.x) * kElems;
   F4 g;
   if (UPDATE) {
-    g = reduce_rows4(rows, n_rows, row_stride, i, (ELEMS == 4 || i + 1 > n + 2) ? n + 2 : i + 1);
+    g = reduce_rows4(rows, 1, row_stride, i, n + 2);
     if (metrics != nullptr) {
 #pragma unroll
-      for (int e = 0; e < ELEMS; ++e) if (i + e >= n && i + e < n + 2) metrics[i + e - n] = g.v[e];   // stay local
+      for (int e = 0; e < kElems; ++e) if (i + e >= n && i + e < n + 2) metrics[i + e - n] = g.v[e];   // stay local
     }
   } else {
-    g = reduce_rows4(buf, 1, 0, i, (ELEMS == 4 || i + 1 > n) ? n : i + 1);
+    g = reduce_rows4(buf, 1, 0, i, n);
   }
   if (i < n) {
-    const long long lim = (ELEMS == 4 || i + 1 > n) ? n : i + 1;   // ELEMS == 1: only element i is mine
-    for (int p = 0; p < c.world; ++p) store4(inbox(c, p, seq, c.rank), g, i, lim);   // peer stores (incl. self)
+    for (int p = 0; p < c.world; ++p) store4(inbox(c, p, seq, c.rank), g, i, n);   // peer stores (incl. self)
   }
-  __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) {
-    delay(c);
-    for (int p = 0; p < c.world; ++p) st_release_sys(flags_ar(c, p, c.rank, blockIdx.x), seq);
+  // ONE system fence (issued by the W publishing lanes together, after the barrier made every thread's peer
+  // stores visible to them), then the W flags go out in parallel as relaxed stores.
+  if (threadIdx.x < c.world) {
+    if (threadIdx.x == 0) delay(c);
+    __syncwarp(__activemask());
+    asm volatile("fence.acq_rel.sys;" ::: "memory");
+    st_relaxed_sys(flags_ar(c, threadIdx.x, c.rank, blockIdx.x), seq);
+    wait_flag(c, flags_ar(c, c.rank, threadIdx.x, blockIdx.x), seq, threadIdx.x);
   }
-  if (threadIdx.x < c.world) wait_flag(c, flags_ar(c, c.rank, threadIdx.x, blockIdx.x), seq, threadIdx.x);
   __syncthreads();
   if (i >= n) return;
   F4 sum; sum.v[0] = sum.v[1] = sum.v[2] = sum.v[3] = 0.0f;
   for (int s = 0; s < c.world; ++s) {   // fixed rank order => identical bits on every rank
-    const F4 t = load4_cg(inbox(c, c.rank, seq, s), i, (ELEMS == 4 || i + 1 > n) ? n : i + 1);
+    const F4 t = load4_cg(inbox(c, c.rank, seq, s), i, n);
 #pragma unroll
     for (int e = 0; e < 4; ++e) sum.v[e] += t.v[e];
   }
 #pragma unroll
-  for (int e = 0; e < ELEMS; ++e) {
+  for (int e = 0; e < kElems; ++e) {
     const long long j = i + e;
     if (j >= n) break;
     if (UPDATE) {
@@ -174,6 +198,101 @@ __global__ void __launch_bounds__(kThreads) oneshot_kernel(
       if (exp_avg_sq) exp_avg_sq[j] = v;
     } else {
       buf[j] = sum.v[e] * scale;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// One-shot, low-latency form ("LL") for the small vectors an LSTM produces (the reference's whole gradient
+// is 56.6 KB): every 8-byte word that crosses NVLink carries 4 bytes of data and the 4-byte sequence
+// number of the call, so the data is its own arrival flag — no fence, no separate flag store, one NVLink
+// one-way latency in total.  A block (rows.cuh geometry: 256 threads, 128 elements) first reduces the
+// backward kernel's per-CTA gradient rows in fixed order, then its 8 warps push the 32 result columns to
+// 8 peers at a time (two 16-byte stores {d0,seq,d1,seq} {d2,seq,d3,seq} per column), then warp s polls the
+// words that source s wrote into this rank's LL inbox, and the first warp adds the W contributions in
+// rank order and runs the optimizer.  Inboxes are double-buffered by the parity of seq like the plain
+// inboxes; a stale word can never match because seq only grows.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint4* ll_slot(const Ctx& c, int owner, uint32_t seq, int src) {
+  return reinterpret_cast<uint4*>(c.base[owner] + c.off_ll) + ((long long)(seq & 1) * c.world + src) * (c.ll_floats / 2);
+}
+__device__ __forceinline__ void st_ll(uint4* p, float a, float b, uint32_t seq) {
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(__float_as_uint(a)), "r"(seq),
+               "r"(__float_as_uint(b)), "r"(seq) : "memory");
+}
+__device__ __forceinline__ uint4 ld_ll(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+
+template <bool UPDATE, bool VEC>
+__global__ void __launch_bounds__(kRowThreads) oneshot_ll_kernel(
+    Ctx c, uint32_t seq, const float* __restrict__ rows, int n_rows, long long n, long long row_stride,
+    float* buf /* UPDATE: params, else in/out vector */, float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq,
+    OptScalars o, float scale, float* __restrict__ metrics) {
+  __shared__ float4 sm[(B200RNN_MAX_PEERS > kRG ? B200RNN_MAX_PEERS : kRG) * kC4];
+  const long long block_e0 = (long long)blockIdx.x * kRowElems;
+  const int col = threadIdx.x % kC4, grp = threadIdx.x / kC4;
+  const long long e0 = block_e0 + 4 * col;            // my column's first element
+  const long long col4 = e0 / 4;                      // float4 index of my column in the vector
+  // ---- phase 0: my rank's vector for these columns ----
+  if (UPDATE) block_reduce_rows<VEC>(rows, n_rows, row_stride, block_e0, n + 2, sm);
+  else block_reduce_rows<VEC>(buf, 1, 0, block_e0, n, sm);
+  const float4 mine = sm[col];
+  if (UPDATE && grp == 0 && metrics != nullptr) {      // row tail (loss sum, correct count) stays local
+    const float mv[4] = {mine.x, mine.y, mine.z, mine.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) if (e0 + e >= n && e0 + e < n + 2) metrics[e0 + e - n] = mv[e];
+  }
+  // ---- phase 1: push (data, seq) words into every peer's LL inbox: warp `grp` serves peers grp, grp+8 ----
+  if (e0 < n) {
+    delay(c);
+    for (int p = grp; p < c.world; p += kRG) {
+      uint4* dst = ll_slot(c, p, seq, c.rank) + 2 * col4;
+      st_ll(dst, mine.x, mine.y, seq);
+      st_ll(dst + 1, mine.z, mine.w, seq);
+    }
+  }
+  __syncthreads();   // sm is about to be reused
+  // ---- phase 2: warp `grp` collects the contributions of sources grp, grp+8 ----
+  if (e0 < n) {
+    for (int src = grp; src < c.world; src += kRG) {
+      const uint4* slot = ll_slot(c, c.rank, seq, src) + 2 * col4;
+      uint4 a = ld_ll(slot), b = ld_ll(slot + 1);
+      if (a.y != seq || a.w != seq || b.y != seq || b.w != seq) {
+        const long long t0 = clock64();
+        do {
+          a = ld_ll(slot); b = ld_ll(slot + 1);
+          if (clock64() - t0 > c.timeout) {
+            atomicOr(reinterpret_cast<unsigned int*>(c.base[c.rank] + c.off_status), 1u << src);
+            break;
+          }
+        } while (a.y != seq || a.w != seq || b.y != seq || b.w != seq);
+      }
+      sm[src * kC4 + col] = make_float4(__uint_as_float(a.x), __uint_as_float(a.z), __uint_as_float(b.x), __uint_as_float(b.z));
+    }
+  }
+  __syncthreads();
+  if (grp != 0 || e0 >= n) return;
+  // ---- phase 3: sum in rank order (identical bits on every rank), optimizer ----
+  float4 sum = sm[col];
+  for (int src = 1; src < c.world; ++src) sum = f4_add(sum, sm[src * kC4 + col]);
+  const float sv[4] = {sum.x, sum.y, sum.z, sum.w};
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const long long j = e0 + e;
+    if (j >= n) break;
+    if (UPDATE) {
+      float p = buf[j];
+      float m = exp_avg ? exp_avg[j] : 0.0f;
+      float v = exp_avg_sq ? exp_avg_sq[j] : 0.0f;
+      apply_update(o, sv[e] * o.grad_scale, p, m, v);
+      buf[j] = p;
+      if (exp_avg) exp_avg[j] = m;
+      if (exp_avg_sq) exp_avg_sq[j] = v;
+    } else {
+      buf[j] = sv[e] * scale;
     }
   }
 }
@@ -507,6 +626,9 @@ extern "C" int64_t b200rnn_comm_layout(b200rnn_comm_ctx* ctx) {
   ctx->off_flags_bar = off; off = align(off + (2 * B200RNN_MAX_PEERS + 4) * 4);   // barrier | bcast | counter
   ctx->off_status = off;    off = align(off + 64);
   ctx->off_inbox = off;     off = align(off + 2 * (int64_t)ctx->world * ctx->inbox_floats * 4);
+  if (ctx->ll_floats <= 0) ctx->ll_floats = 64 * 1024;     // LL one-shot: vectors up to 256 KB
+  ctx->ll_floats = (ctx->ll_floats + 3) & ~int64_t(3);
+  ctx->off_ll = off;        off = align(off + 2 * (int64_t)ctx->world * ctx->ll_floats * 8);   // (data, seq) words
   ctx->off_heap = off;      off = align(off + ctx->heap_bytes);
   return off;
 }
@@ -518,26 +640,34 @@ static int launch_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, const flo
   OptScalars o{};
   if (update) o = make_opt_scalars(opt);
   const int64_t row_stride = n + 2;
-  // several gradient rows to reduce (the fused training step): 1 element per thread keeps 4x more
-  // threads on the row reduction; a single row: 4 elements per thread with 128-bit peer stores
-  const int one_elems = (update && n_rows > 1) ? 1 : kElems;
-  const int64_t one_blocks = ((update ? n + 2 : n) + kThreads * one_elems - 1) / (kThreads * one_elems);
+  const bool ll_fits = ((n + 3) & ~int64_t(3)) <= ctx->ll_floats;
   if (algo == B200RNN_ALGO_AUTO) {
-    // one-shot moves W*n floats per rank but pays a single NVLink latency; two-shot moves
-    // 2(W-1)/W*n but pays two latencies and two grid barriers.  Crossover from the measured sweep
-    // (bench/allreduce_sweep.py, profiles/).
-    // Measured (profiles/r1_allreduce_sweep_n{2,8}.md): one-shot wins while W * bytes <= ~128 KiB
-    // (W = 2: <= 64 KiB, W = 8: <= 16 KiB); above that its W-fold traffic and W flags per block lose.
-    algo = (n * 4 * ctx->world <= 128 * 1024 || ctx->world == 1 || heap_off < 0) ? B200RNN_ALGO_ONESHOT : B200RNN_ALGO_TWOSHOT;
+    // Fallback rule for callers without a measured table (the Python layer passes an explicit choice from
+    // profiles/allreduce_table.json): LL while the vector fits its inbox and W * bytes stays small (its
+    // traffic is 2 W n), flag-based one-shot up to ~128 KiB of W * bytes, two-shot above.
+    if (ctx->world == 1 || (ll_fits && n * 4 * ctx->world <= 2 * 1024 * 1024)) algo = B200RNN_ALGO_LL;
+    else algo = (n * 4 * ctx->world <= 128 * 1024 || heap_off < 0) ? B200RNN_ALGO_ONESHOT : B200RNN_ALGO_TWOSHOT;
   }
-  if (algo == B200RNN_ALGO_ONESHOT) {
+  if (algo == B200RNN_ALGO_LL) {
+    B200_REQUIRE(ll_fits, B200RNN_ETOOBIG, "comm LL one-shot: n=%lld exceeds the LL inbox capacity %lld",
+                 (long long)n, (long long)ctx->ll_floats);
+    const int64_t blocks = ((update ? n + 2 : n) + kRowElems - 1) / kRowElems;
+    const bool vec = update ? rows_vectorizable(rows, row_stride) : ((reinterpret_cast<uintptr_t>(buf) & 15) == 0);
+#define B200_LL(UPD, VEC) oneshot_ll_kernel<UPD, VEC><<<(unsigned)blocks, kRowThreads, 0, s>>>( \
+        c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics)
+    if (update) { if (vec) B200_LL(true, true); else B200_LL(true, false); }
+    else { if (vec) B200_LL(false, true); else B200_LL(false, false); }
+#undef B200_LL
+  } else if (algo == B200RNN_ALGO_ONESHOT) {
+    B200_REQUIRE(!update || n_rows == 1, B200RNN_EINVAL,
+                 "comm one-shot: reduce the %d gradient rows first (b200rnn_reduce_rows) or use the LL form", n_rows);
+    const int64_t one_blocks = ((update ? n + 2 : n) + kBlockElems - 1) / kBlockElems;
     B200_REQUIRE(one_blocks <= ctx->max_blocks, B200RNN_ETOOBIG, "comm one-shot: %lld blocks exceed max_blocks=%d",
                  (long long)one_blocks, ctx->max_blocks);
     B200_REQUIRE(n <= ctx->inbox_floats, B200RNN_ETOOBIG, "comm one-shot: n=%lld exceeds inbox capacity %lld",
                  (long long)n, (long long)ctx->inbox_floats);
-    if (update && one_elems == 1) oneshot_kernel<true, 1><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
-    else if (update) oneshot_kernel<true, 4><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
-    else oneshot_kernel<false, 4><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n_rows, n, row_stride, buf, m, v, o, scale, metrics);
+    if (update) oneshot_kernel<true><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n, row_stride, buf, m, v, o, scale, metrics);
+    else oneshot_kernel<false><<<(unsigned)one_blocks, kThreads, 0, s>>>(c, seq, rows, n, row_stride, buf, m, v, o, scale, metrics);
   } else {
     int64_t shard = (n + ctx->world - 1) / ctx->world;
     shard = (shard + 3) & ~int64_t(3);                       // 16-byte aligned shard starts
@@ -575,8 +705,18 @@ extern "C" int b200rnn_comm_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq,
   int rc = check_ctx(ctx, "comm_allreduce");
   if (rc) return rc;
   B200_REQUIRE(buf && n > 0, B200RNN_EINVAL, "comm_allreduce: bad argument");
-  return launch_allreduce(ctx, seq, nullptr, 0, n, buf, -1, nullptr, nullptr, nullptr, scale, nullptr,
-                          B200RNN_ALGO_ONESHOT, false, (cudaStream_t)stream);
+  const bool ll = ((n + 3) & ~int64_t(3)) <= ctx->ll_floats && n * 4 * ctx->world <= 2 * 1024 * 1024;
+  return launch_allreduce(ctx, seq, nullptr, 1, n, buf, -1, nullptr, nullptr, nullptr, scale, nullptr,
+                          ll ? B200RNN_ALGO_LL : B200RNN_ALGO_ONESHOT, false, (cudaStream_t)stream);
+}
+extern "C" int b200rnn_comm_allreduce_algo(const b200rnn_comm_ctx* ctx, uint32_t seq, float* buf, int64_t n, float scale,
+                                           int32_t algo, void* stream) {
+  int rc = check_ctx(ctx, "comm_allreduce_algo");
+  if (rc) return rc;
+  B200_REQUIRE(buf && n > 0 && (algo == B200RNN_ALGO_LL || algo == B200RNN_ALGO_ONESHOT), B200RNN_EINVAL,
+               "comm_allreduce_algo: bad argument (only the one-shot forms work on a vector outside the heap)");
+  return launch_allreduce(ctx, seq, nullptr, 1, n, buf, -1, nullptr, nullptr, nullptr, scale, nullptr, algo, false,
+                          (cudaStream_t)stream);
 }
 
 extern "C" int b200rnn_comm_broadcast(const b200rnn_comm_ctx* ctx, uint32_t seq, int64_t heap_off, int64_t bytes,

@@ -2,6 +2,7 @@
 // (standalone form), deterministic row reduction, K6 fused optimizer, L2 flush.
 #include "common.cuh"
 #include "optim.cuh"
+#include "rows.cuh"
 #include <math.h>
 
 namespace b200rnn {
@@ -47,28 +48,39 @@ __global__ void reduce_rows_kernel(const float* __restrict__ rows, int n_rows, i
 }
 
 // ---- K6 fused optimizer (W = 1 form; the multi-GPU form lives in comm/) ----
-__global__ void fused_update_kernel(const float* __restrict__ rows, int n_rows, int64_t n_params,
-                                    float* __restrict__ params, float* __restrict__ exp_avg,
-                                    float* __restrict__ exp_avg_sq, OptScalars o,
-                                    float* __restrict__ grad_out, float* __restrict__ metrics) {
+// One block = 128 consecutive elements: fixed-order sum of the gradient rows (rows.cuh), then the
+// optimizer on 4 elements per thread of the first warp.
+template <bool VEC>
+__global__ void __launch_bounds__(kRowThreads) fused_update_kernel(
+    const float* __restrict__ rows, int n_rows, int64_t n_params, float* __restrict__ params,
+    float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq, OptScalars o,
+    float* __restrict__ grad_out, float* __restrict__ metrics) {
+  __shared__ float4 sm[kRowThreads];
   const int64_t row_floats = n_params + 2;
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= row_floats) return;
-  float acc = 0.0f;
-  for (int r = 0; r < n_rows; ++r) acc += rows[(int64_t)r * row_floats + i];
-  if (i >= n_params) {
-    if (metrics != nullptr) metrics[i - n_params] = acc;
-    return;
+  const int64_t block_e0 = (int64_t)blockIdx.x * kRowElems;
+  block_reduce_rows<VEC>(rows, n_rows, row_floats, block_e0, row_floats, sm);
+  if (threadIdx.x >= kC4) return;
+  const int64_t e0 = block_e0 + 4 * threadIdx.x;
+  const float4 s4 = sm[threadIdx.x];
+  const float acc[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int64_t i = e0 + e;
+    if (i >= row_floats) break;
+    if (i >= n_params) {
+      if (metrics != nullptr) metrics[i - n_params] = acc[e];
+      continue;
+    }
+    const float g = acc[e] * o.grad_scale;
+    if (grad_out != nullptr) grad_out[i] = g;
+    float p = params[i];
+    float m = exp_avg ? exp_avg[i] : 0.0f;
+    float v = exp_avg_sq ? exp_avg_sq[i] : 0.0f;
+    apply_update(o, g, p, m, v);
+    params[i] = p;
+    if (exp_avg) exp_avg[i] = m;
+    if (exp_avg_sq) exp_avg_sq[i] = v;
   }
-  const float g = acc * o.grad_scale;
-  if (grad_out != nullptr) grad_out[i] = g;
-  float p = params[i];
-  float m = exp_avg ? exp_avg[i] : 0.0f;
-  float v = exp_avg_sq ? exp_avg_sq[i] : 0.0f;
-  apply_update(o, g, p, m, v);
-  params[i] = p;
-  if (exp_avg) exp_avg[i] = m;
-  if (exp_avg_sq) exp_avg_sq[i] = v;
 }
 
 // ---- K5 head, standalone: one warp per sample ----
@@ -169,10 +181,13 @@ extern "C" int b200rnn_fused_update(const float* rows, int32_t n_rows, int64_t n
   B200_REQUIRE(!(opt->kind == 1 && opt->momentum != 0.0f && !exp_avg), B200RNN_EINVAL,
                "fused_update: SGD momentum needs a momentum buffer (exp_avg)");
   const OptScalars o = make_opt_scalars(opt);
-  const int threads = 256;
-  const int64_t blocks = (n_params + 2 + threads - 1) / threads;
-  fused_update_kernel<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(
-      rows, n_rows, n_params, params, exp_avg, exp_avg_sq, o, grad_out, metrics);
+  const int64_t blocks = (n_params + 2 + kRowElems - 1) / kRowElems;
+  if (rows_vectorizable(rows, n_params + 2))
+    fused_update_kernel<true><<<(unsigned)blocks, kRowThreads, 0, (cudaStream_t)stream>>>(
+        rows, n_rows, n_params, params, exp_avg, exp_avg_sq, o, grad_out, metrics);
+  else
+    fused_update_kernel<false><<<(unsigned)blocks, kRowThreads, 0, (cudaStream_t)stream>>>(
+        rows, n_rows, n_params, params, exp_avg, exp_avg_sq, o, grad_out, metrics);
   B200_CHECK_LAUNCH();
   return B200RNN_OK;
 }

@@ -138,6 +138,33 @@ int b200rnn_gru_bwd_dx(const b200rnn_model_desc* d, const float* params,
                        float loss_scale, const float* d_out, const float* d_hn,
                        float* scratch, float* dx, void* stream);
 
+/* Training-loop forms of the fused forward / backward (LSTM and GRU): the same kernels with two extras.
+ *  - idx (nullable, [B] int64): batch row b is row idx[b] of x and of labels, i.e. x / labels are the
+ *    whole device-resident dataset and idx is the sampler's slice for this step — the K11 gather folded
+ *    into the kernels' own loaders (DataLoader + DistributedSampler, src/motion/trainer/base.py:56-60,107).
+ *  - flags: hand-over of the layer-wavefront sentinels between consecutive calls on the same buffers,
+ *    which removes the fill launch in front of a wavefront kernel.
+ *      B200RNN_STEP_ARMED  forward: h_seq of the layers below the top already holds the sentinel
+ *                          everywhere; backward: so do the inter-layer dx buffers in `scratch`.
+ *      B200RNN_STEP_REARM  backward only: write the sentinel back over every h_seq element of the lower
+ *                          layers and every dx element once consumed, so that the NEXT forward / backward
+ *                          on the same stash / scratch may be called with B200RNN_STEP_ARMED.  The stash is
+ *                          therefore not const here, and h_seq of the lower layers is gone afterwards.
+ *    A buffer is armed only by such a backward; any other call that writes it (a forward, a backward
+ *    without REARM) disarms it.  With flags == 0 these are b200rnn_lstm_fwd / b200rnn_lstm_bwd plus idx. */
+#define B200RNN_STEP_ARMED 1
+#define B200RNN_STEP_REARM 2
+int b200rnn_lstm_fwd_ex(const b200rnn_model_desc* d, const float* params, const float* x, const int64_t* idx,
+                        float* stash, int32_t training, int32_t flags, void* stream);
+int b200rnn_lstm_bwd_ex(const b200rnn_model_desc* d, const float* params, const float* x, const int64_t* idx,
+                        float* stash, const int64_t* labels, float loss_scale, const float* d_out,
+                        const float* d_hn, const float* d_cn, float* scratch, int32_t flags, void* stream);
+int b200rnn_gru_fwd_ex(const b200rnn_model_desc* d, const float* params, const float* x, const int64_t* idx,
+                       float* stash, int32_t training, int32_t flags, void* stream);
+int b200rnn_gru_bwd_ex(const b200rnn_model_desc* d, const float* params, const float* x, const int64_t* idx,
+                       float* stash, const int64_t* labels, float loss_scale, const float* d_out,
+                       const float* d_hn, float* scratch, int32_t flags, void* stream);
+
 /* Capacity of the scratch array compiled into the library for b200rnn_lstm_bwd_static. */
 #define B200RNN_STATIC_SCRATCH_FLOATS (4 * 1024 * 1024)
 
@@ -156,7 +183,8 @@ int b200rnn_gru_bwd_dx(const b200rnn_model_desc* d, const float* params,
  *    refused with B200RNN_ETOOBIG (message in b200rnn_last_error()); use b200rnn_lstm_bwd.
  *  - The first call on each device looks up the array's device address
  *    (cudaGetSymbolAddress with that device current) and caches it; make that first call
- *    outside any stream capture.  Later calls only launch kernels.
+ *    outside any stream capture.  Later calls only launch kernels.  The device that owns
+ *    `stream` must be the current device (checked; B200RNN_EINVAL otherwise).
  *  - All calls on a device share the one array and it keeps the previous call's contents.
  *    Nothing in it needs clearing (each element is written before it is read within a call),
  *    but two calls that overlap on the GPU (different streams, no dependency) race on it:
@@ -253,9 +281,10 @@ int b200rnn_gru_persist_bwd(int32_t T, int32_t B, int32_t H, const float* gates,
                             void* dG_bf16, float* dG2, void* dG2_bf16, void* stream_img, void* sync, void* stream);
 int b200rnn_persist_status(int32_t* status);
 
-/* Non-zero once a bounded wait of the small-hidden family's layer-wavefront mode timed out (a
- * consumer CTA never saw its producer's values; results of that call are then garbage).
- * B200RNN_WAVE=0 keeps the layers of a batch tile in one CTA, in sequence. */
+/* Status word of the small-hidden family, sticky since load.  Bit 0: a bounded wait of the
+ * layer-wavefront mode timed out (a consumer CTA never saw its producer's values; results of that
+ * call are garbage; B200RNN_WAVE=0 keeps the layers of a batch tile in one CTA, in sequence).
+ * Bit 1: the fused head met a label outside [0, num_classes) (it was treated as class 0). */
 int b200rnn_wave_status(int32_t* status);
 /* Whether the small-hidden forward / backward of this shape is launched as a layer wavefront (each then
  * issues one extra small kernel, the sentinel pre-fill, before the main one). */
@@ -327,15 +356,18 @@ typedef struct {
   int64_t inbox_floats;     /* capacity per (parity, source) inbox */
   int64_t timeout_cycles;   /* watchdog for flag waits (0 = default) */
   int64_t heap_bytes;
+  int64_t ll_floats;        /* capacity (floats, per (parity, source)) of the low-latency one-shot inbox;
+                               0 = default (64 Ki floats) */
   /* byte offsets inside a region (identical on every rank) */
-  int64_t off_flags_ar, off_flags_pr, off_flags_sig, off_flags_bar, off_status, off_inbox, off_heap;
+  int64_t off_flags_ar, off_flags_pr, off_flags_sig, off_flags_bar, off_status, off_inbox, off_heap, off_ll;
   void* base[B200RNN_MAX_PEERS];
 } b200rnn_comm_ctx;
 
 /* Fills the off_* fields from world / max_blocks / inbox_floats / heap_bytes; returns region bytes. */
 int64_t b200rnn_comm_layout(b200rnn_comm_ctx* ctx);
 
-enum { B200RNN_ALGO_AUTO = 0, B200RNN_ALGO_ONESHOT = 1, B200RNN_ALGO_TWOSHOT = 2, B200RNN_ALGO_NVLS = 3 };
+enum { B200RNN_ALGO_AUTO = 0, B200RNN_ALGO_ONESHOT = 1, B200RNN_ALGO_TWOSHOT = 2, B200RNN_ALGO_NVLS = 3,
+       B200RNN_ALGO_LL = 4 /* one-shot, (data, seq) words: no fence, no flags; vectors <= ll_floats */ };
 
 /* K7: ONE kernel = fixed-order reduction of the n_rows local gradient rows + all-reduce over
  * NVLink peer memory (one-shot: every rank pushes its vector into every peer's inbox; two-shot:
@@ -360,6 +392,9 @@ int b200rnn_comm_allreduce_update_nvls(const b200rnn_comm_ctx* ctx, void* mc_bas
  * the optimizer epilogue.  Shares the seq counter with b200rnn_comm_allreduce_update. */
 int b200rnn_comm_allreduce(const b200rnn_comm_ctx* ctx, uint32_t seq, float* buf, int64_t n,
                            float scale, void* stream);
+/* Same with an explicit one-shot form (B200RNN_ALGO_LL or B200RNN_ALGO_ONESHOT): what the latency sweep times. */
+int b200rnn_comm_allreduce_algo(const b200rnn_comm_ctx* ctx, uint32_t seq, float* buf, int64_t n,
+                                float scale, int32_t algo, void* stream);
 /* K8: broadcast `bytes` at heap offset `heap_off` from root's heap into every rank's heap. */
 int b200rnn_comm_broadcast(const b200rnn_comm_ctx* ctx, uint32_t seq, int64_t heap_off, int64_t bytes,
                            int32_t root, void* stream);

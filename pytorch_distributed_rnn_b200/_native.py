@@ -47,8 +47,10 @@ class CommCtx(C.Structure):
     _fields_ = [
         ("rank", C.c_int32), ("world", C.c_int32), ("max_blocks", C.c_int32), ("delay_ns", C.c_int32),
         ("inbox_floats", C.c_int64), ("timeout_cycles", C.c_int64), ("heap_bytes", C.c_int64),
+        ("ll_floats", C.c_int64),
         ("off_flags_ar", C.c_int64), ("off_flags_pr", C.c_int64), ("off_flags_sig", C.c_int64),
         ("off_flags_bar", C.c_int64), ("off_status", C.c_int64), ("off_inbox", C.c_int64), ("off_heap", C.c_int64),
+        ("off_ll", C.c_int64),
         ("base", C.c_void_p * MAX_PEERS),
     ]
 
@@ -87,6 +89,10 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_lstm_bwd": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
         "b200rnn_gru_fwd": (i32, [P(ModelDesc), vp, vp, vp, i32, vp]),
         "b200rnn_gru_bwd": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp]),
+        "b200rnn_lstm_fwd_ex": (i32, [P(ModelDesc), vp, vp, vp, vp, i32, i32, vp]),
+        "b200rnn_lstm_bwd_ex": (i32, [P(ModelDesc), vp, vp, vp, vp, vp, f32, vp, vp, vp, vp, i32, vp]),
+        "b200rnn_gru_fwd_ex": (i32, [P(ModelDesc), vp, vp, vp, vp, i32, i32, vp]),
+        "b200rnn_gru_bwd_ex": (i32, [P(ModelDesc), vp, vp, vp, vp, vp, f32, vp, vp, vp, i32, vp]),
         "b200rnn_rnn_persist_supported": (i32, [P(ModelDesc)]),
         "b200rnn_persist_status": (i32, [P(i32)]),
         "b200rnn_wave_status": (i32, [P(i32)]),
@@ -128,6 +134,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_comm_allreduce_update": (i32, [P(CommCtx), C.c_uint32, vp, i32, i64, vp, i64, vp, vp, P(OptimDesc), vp, i32, vp]),
         "b200rnn_comm_allreduce_update_nvls": (i32, [P(CommCtx), vp, C.c_uint32, vp, i32, i64, vp, i64, i64, vp, vp, P(OptimDesc), vp, vp]),
         "b200rnn_comm_allreduce": (i32, [P(CommCtx), C.c_uint32, vp, i64, f32, vp]),
+        "b200rnn_comm_allreduce_algo": (i32, [P(CommCtx), C.c_uint32, vp, i64, f32, i32, vp]),
         "b200rnn_comm_broadcast": (i32, [P(CommCtx), C.c_uint32, i64, i64, i32, vp]),
         "b200rnn_comm_put": (i32, [P(CommCtx), C.c_uint32, i32, vp, i64, i64, vp]),
         "b200rnn_comm_wait": (i32, [P(CommCtx), C.c_uint32, i32, vp]),
@@ -192,6 +199,8 @@ def device_status() -> dict:
 def assert_device_healthy() -> None:
     """Raise if any in-kernel watchdog fired since the library was loaded (results of that call are garbage)."""
     bad = {k: v for k, v in device_status().items() if v != 0}
+    if bad.get("wave", 0) & 2:
+        raise NativeError("fused head: a label outside [0, num_classes) reached the loss (status %r)" % (bad,))
     if bad:
         raise NativeError(f"in-kernel watchdog fired: {bad} (a wait for a peer CTA / TMA / MMA timed out; "
                           "see INTEGRATION.md: B200RNN_PERSIST / B200RNN_WAVE)")

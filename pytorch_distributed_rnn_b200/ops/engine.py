@@ -1,5 +1,9 @@
 """FusedTrainEngine — the whole training step of the motion classifier as 3 kernel launches.
 
+(Exactly three in steady state, at every world size: the batch is read through the sampler's index
+slice by the kernels' own loaders, the layer-wavefront sentinels are put back by their consumers,
+and the reduction of the per-CTA gradient rows is the first phase of the update / all-reduce kernel.)
+
 The reference's hot loop (src/motion/trainer/base.py:103-130) is, per batch:
 ``zero_grad -> model(data) -> CrossEntropyLoss -> argmax/eq/sum -> backward -> Adam.step``
 — hundreds of ATen kernel launches, two host syncs (``loss.item()`` twice) and, under DDP,
@@ -11,7 +15,7 @@ a blocking all-reduce inside ``backward``.  Here the same step is:
    deterministic reduction of the per-CTA gradient rows, the in-kernel NVLink all-reduce,
    gradient averaging and the Adam/SGD step (K6+K7);
 
-plus an optional K11 gather in front when the batch comes from a device-resident dataset.
+The K11 gather of a device-resident dataset is folded into launches 1 and 2 (``train_step_gather``).
 Nothing in the step synchronises with the host; loss / correct-count land in a device ring
 buffer that the trainer reads when it wants to log.
 """
@@ -46,12 +50,18 @@ class FusedTrainEngine:
         self.fwd_kind = os.environ.get("B200RNN_FWD", "ffma")
         self.model = model
         lib = self.lib
+        self._fwd_ex = None   # forward that reads the batch through an index slice and takes hand-over flags
         if model.cell == "gru":   # GRU members of the fused family (no tcgen05 variant)
             self._fwd = lib.b200rnn_gru_fwd
-            self._bwd = lambda d, p, x, st, y, scale, scratch, sp: lib.b200rnn_gru_bwd(d, p, x, st, y, scale, None, None, scratch, sp)
+            self._fwd_ex = lib.b200rnn_gru_fwd_ex
+            self._bwd_ex = lambda d, p, x, idx, st, y, scale, scratch, fl, sp: lib.b200rnn_gru_bwd_ex(
+                d, p, x, idx, st, y, scale, None, None, scratch, fl, sp)
         else:
             self._fwd = lib.b200rnn_lstm_fwd_tc if self.fwd_kind == "tc" else lib.b200rnn_lstm_fwd
-            self._bwd = lambda d, p, x, st, y, scale, scratch, sp: lib.b200rnn_lstm_bwd(d, p, x, st, y, scale, None, None, None, scratch, sp)
+            if self.fwd_kind != "tc":
+                self._fwd_ex = lib.b200rnn_lstm_fwd_ex
+            self._bwd_ex = lambda d, p, x, idx, st, y, scale, scratch, fl, sp: lib.b200rnn_lstm_bwd_ex(
+                d, p, x, idx, st, y, scale, None, None, None, scratch, fl, sp)
         self.device = p0.device
         self.comm = comm
         self.arena = arena if arena is not None else (optimizer.arena if optimizer is not None else ParamArena(model))
@@ -101,9 +111,10 @@ class FusedTrainEngine:
             _native.check(self.lib.b200rnn_rnn_small_tiling(C.byref(d), C.byref(rb), C.byref(nc)), "tiling")
             buf = dict(
                 desc=d, n_cta=nc.value, rows_per_cta=rb.value,
-                # kernels per step: forward, backward, reduce+update (+ one sentinel pre-fill per wavefront kernel)
-                fwd_launches=1 + self._fwd_wave(d),
-                step_launches=3 + self._fwd_wave(d) + int(self.lib.b200rnn_rnn_small_bwd_wave(C.byref(d))),
+                # kernels per step: forward, backward, reduce+update; a wavefront kernel whose buffers do not hold
+                # the sentinel yet (first use, or after an evaluation) is preceded by one fill launch
+                fwd_wave=bool(self._fwd_wave(d)), bwd_wave=bool(self.lib.b200rnn_rnn_small_bwd_wave(C.byref(d))),
+                h_armed=False, dx_armed=False,
                 stash=torch.empty(self.lib.b200rnn_rnn_stash_floats(C.byref(d)), dtype=torch.float32, device=self.device),
                 scratch=torch.empty(self.lib.b200rnn_rnn_bwd_scratch_floats(C.byref(d)), dtype=torch.float32, device=self.device),
                 x=None, y=None)
@@ -111,18 +122,46 @@ class FusedTrainEngine:
         return buf
 
     # -- one optimisation step on a device batch --
-    def train_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
-        """x [B,T,I] fp32, y [B] or [B,1] int64, both on the engine's device.
+    ARMED, REARM = 1, 2   # B200RNN_STEP_* (include/b200rnn.h)
+
+    def train_step(self, x: torch.Tensor, y: torch.Tensor, idx: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """x [B,T,I] fp32, y [B] or [B,1] int64, both on the engine's device.  With ``idx`` ([B] int64 on the
+        device) x / y are the whole device-resident dataset and batch row b is row ``idx[b]`` of them.
         Returns a device view [2] = (sum of per-sample CE losses, correct count) for this batch."""
-        B, T, _ = x.shape
+        T = x.shape[1]
+        B = x.shape[0] if idx is None else idx.numel()
+        if x.dtype != torch.float32 or not x.is_contiguous() or x.device != self.device:
+            raise ValueError("train_step: x must be a contiguous fp32 tensor on the engine's device")
+        y = y.reshape(-1)
+        if y.dtype != torch.int64 or not y.is_contiguous() or y.device != self.device:
+            raise ValueError("train_step: labels must be a contiguous int64 tensor on the engine's device")
+        if idx is not None and (idx.dtype != torch.int64 or not idx.is_contiguous() or idx.device != self.device):
+            raise ValueError("train_step: idx must be a contiguous int64 tensor on the engine's device")
         buf = self._get(B, T)
         d = buf["desc"]
-        y = y.reshape(-1)
         sp = _native.stream_ptr(self.device)
         a, opt = self.arena, self.optimizer
-        _native.check(self._fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 1, sp), "lstm_fwd")
-        _native.check(self._bwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(),
-                                                y.data_ptr(), 1.0 / B, buf["scratch"].data_ptr(), sp), "lstm_bwd")
+        n_launch = 3
+        if self._fwd_ex is None:   # tcgen05 forward: plain entry point, explicit gather in front
+            if idx is not None:
+                x, y = self._gather(buf, x, y, idx)
+                idx = None
+                n_launch += 1
+            _native.check(self._fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 1, sp), "lstm_fwd")
+            buf["h_armed"] = False
+        else:
+            f_fl = self.ARMED if buf["h_armed"] else 0
+            n_launch += int(buf["fwd_wave"] and not buf["h_armed"])
+            _native.check(self._fwd_ex(C.byref(d), a.flat.data_ptr(), x.data_ptr(), _native.ptr(idx),
+                                       buf["stash"].data_ptr(), 1, f_fl, sp), "rnn_fwd")
+            buf["h_armed"] = False
+        # the consumers put the wavefront sentinels back, so the next step needs no fill launch
+        rearm = self._fwd_ex is not None and (buf["fwd_wave"] or buf["bwd_wave"])
+        b_fl = (self.ARMED if buf["dx_armed"] else 0) | (self.REARM if rearm else 0)
+        n_launch += int(buf["bwd_wave"] and not buf["dx_armed"])
+        _native.check(self._bwd_ex(C.byref(d), a.flat.data_ptr(), x.data_ptr(), _native.ptr(idx), buf["stash"].data_ptr(),
+                                   y.data_ptr(), 1.0 / B, buf["scratch"].data_ptr(), b_fl, sp), "rnn_bwd")
+        buf["h_armed"], buf["dx_armed"] = rearm, rearm and buf["bwd_wave"]
         opt.step_count += 1
         slot = self.metrics[self.n_steps % self.METRIC_RING]
         o = opt.desc(grad_scale=1.0 / self.world)
@@ -132,23 +171,24 @@ class FusedTrainEngine:
                 opt.exp_avg_sq.data_ptr(), C.byref(o), None, slot.data_ptr(), sp), "fused_update")
         else:
             self.comm.allreduce_update(buf["scratch"], buf["n_cta"], a, opt, o, slot)
-        _native.count_launch(buf["step_launches"])
+        _native.count_launch(n_launch)
         self.n_steps += 1
         return slot
 
-    def train_step_gather(self, feats: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
-        """K11 gather from a device-resident dataset (feats [N,T,I], labels [N] or [N,1]) then train_step."""
-        B = idx.numel()
-        T, I = feats.shape[1], feats.shape[2]
-        buf = self._get(B, T)
+    def _gather(self, buf: dict, feats: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor):
+        B, T, I = idx.numel(), feats.shape[1], feats.shape[2]
         if buf["x"] is None:
             buf["x"] = torch.empty(B, T, I, dtype=torch.float32, device=self.device)
             buf["y"] = torch.empty(B, dtype=torch.int64, device=self.device)
         _native.check(self.lib.b200rnn_gather_batch(feats.data_ptr(), labels.data_ptr(), idx.data_ptr(), B, T * I,
                                                     buf["x"].data_ptr(), buf["y"].data_ptr(),
                                                     _native.stream_ptr(self.device)), "gather_batch")
-        _native.count_launch()
-        return self.train_step(buf["x"], buf["y"])
+        return buf["x"], buf["y"]
+
+    def train_step_gather(self, feats: torch.Tensor, labels: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+        """Train on rows ``idx`` of a device-resident dataset (feats [N,T,I], labels [N] or [N,1]): the gather of
+        the reference's DataLoader (src/motion/trainer/base.py:107) happens inside the forward / backward loaders."""
+        return self.train_step(feats, labels, idx)
 
     def train_step_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> Tuple[float, int]:
         """End-to-end step from host memory: H2D copy of the batch (pass pinned tensors for an async
@@ -237,8 +277,9 @@ class FusedTrainEngine:
         a, m = self.arena, self.model
         H, L = m.hidden_dim, m.layer_dim
         _native.check(self._fwd(C.byref(d), a.flat.data_ptr(), x.data_ptr(), buf["stash"].data_ptr(), 0, sp), "lstm_fwd")
+        buf["h_armed"] = False   # the stash now holds activations, not sentinels
         h_last = buf["stash"][((L - 1) * T + (T - 1)) * B * H:][:B * H]
         _native.check(self.lib.b200rnn_head_fwd(h_last.data_ptr(), H, m.fc.weight.data_ptr(), m.fc.bias.data_ptr(),
                                                 y.data_ptr(), B, H, m.output_dim, None, self.eval_metrics.data_ptr(), sp), "head_fwd")
-        _native.count_launch(2 + buf["fwd_launches"])
+        _native.count_launch(3 + int(buf["fwd_wave"] and self._fwd_ex is not None))
         return self.eval_metrics[:2]

@@ -30,8 +30,10 @@ def free_port() -> int:
 
 
 def launch(cmd: Sequence[str], nproc: int, timeout: Optional[float] = None, env: Optional[dict] = None,
-           capture: bool = True, master_port: Optional[int] = None) -> List[subprocess.CompletedProcess]:
-    """Run ``cmd`` as ``nproc`` ranks; returns one CompletedProcess per rank (rank order)."""
+           capture: bool = True, master_port: Optional[int] = None,
+           fail_fast: bool = True) -> List[subprocess.CompletedProcess]:
+    """Run ``cmd`` as ``nproc`` ranks; returns one CompletedProcess per rank (rank order).  With ``fail_fast`` a
+    rank that exits non-zero takes the others down (like mpirun); without it every rank runs to its own end."""
     port = master_port or free_port()
     procs = []
     for r in range(nproc):
@@ -56,7 +58,7 @@ def launch(cmd: Sequence[str], nproc: int, timeout: Optional[float] = None, env:
                 out, err = p.communicate()
                 err = (err or "") + f"\n[launch] rank {r} timed out"
             results[r] = subprocess.CompletedProcess(p.args, p.returncode, out, err)
-            if p.returncode != 0:
+            if p.returncode != 0 and fail_fast:
                 failed = True
             if failed:
                 for q in procs:

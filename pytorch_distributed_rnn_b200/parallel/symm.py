@@ -42,10 +42,37 @@ class _External:
         self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
 
 
+ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS, ALGO_LL = 0, 1, 2, 3, 4
+ALGO_NAMES = {ALGO_ONESHOT: "oneshot", ALGO_TWOSHOT: "twoshot", ALGO_NVLS: "nvls", ALGO_LL: "ll"}
+
+# Per-world-size crossovers between the all-reduce variants (vector bytes).  The defaults are what the
+# round-1 sweeps suggested; `bench/allreduce_sweep.py --write-table` replaces them with the measured
+# crossovers of the box it ran on and persists them in profiles/allreduce_table.json, which is loaded here
+# (B200RNN_ALGO_TABLE points elsewhere) — SURVEY §5.8 item 3: "picked per bucket from a measured table".
+DEFAULT_TABLE = {"ll_max_bytes": 256 << 10, "oneshot_max_bytes": 0, "nvls_min_bytes": 1 << 20}
+
+
+def load_algo_table(world: int, path: Optional[str] = None) -> dict:
+    import json
+    from pathlib import Path
+    table = dict(DEFAULT_TABLE)
+    table["source"] = "defaults"
+    p = Path(path or os.environ.get("B200RNN_ALGO_TABLE") or
+             Path(__file__).resolve().parents[2] / "profiles" / "allreduce_table.json")
+    try:
+        doc = json.loads(p.read_text())
+        row = doc.get("worlds", {}).get(str(world))
+        if row:
+            table.update({k: int(v) for k, v in row.items() if k in DEFAULT_TABLE})
+            table["source"] = str(p)
+    except (OSError, ValueError):
+        pass
+    return table
+
+
 class SymmComm:
     kind = "symm"
     MAILBOX_BYTES = 1 << 16  # per source rank, for put/get
-    NVLS_MIN_BYTES = 1 << 20  # auto: in-switch reduction above this vector size (measured crossover)
 
     def __init__(self, info: Optional[RankInfo] = None, inbox_floats: Optional[int] = None,
                  heap_bytes: Optional[int] = None, max_blocks: int = 1 << 16, delay_ns: int = 0,
@@ -79,7 +106,9 @@ class SymmComm:
         ctx = CommCtx()
         delay_ns = delay_ns or int(os.environ.get("B200RNN_DELAY_NS", "0"))
         ctx.rank, ctx.world, ctx.max_blocks, ctx.delay_ns = self.rank, self.world, max_blocks, delay_ns
+        # watchdog of the in-kernel waits: B200RNN_COMM_TIMEOUT_MS (default 60 s, resolved natively when 0 here)
         ctx.inbox_floats, ctx.timeout_cycles, ctx.heap_bytes = inbox_floats, 0, heap_bytes
+        ctx.ll_floats = int(os.environ.get("B200RNN_LL_FLOATS", 64 << 10))
         region = self.lib.b200rnn_comm_layout(C.byref(ctx))
         if region <= 0:
             raise _native.NativeError("comm_layout failed")
@@ -130,6 +159,8 @@ class SymmComm:
         self._seq_put = [0] * self.world
         self._seq_get = [0] * self.world
         self.algo = int(os.environ.get("B200RNN_ALGO", "0"))
+        self.table = load_algo_table(self.world)
+        self.last_algo = None
 
     # ---- symmetric heap ----
     def heap_alloc(self, nbytes: int, align: int = 256) -> int:
@@ -165,47 +196,63 @@ class SymmComm:
     def _sp(self):
         return _native.stream_ptr(self.device)
 
+    def pick_algo(self, n: int, in_heap: bool, nvls_ok: bool) -> int:
+        """Variant for an n-float vector: the forced one (B200RNN_ALGO) or the measured table's."""
+        nbytes, t = n * 4, self.table
+        ll_fits = (n + 3) // 4 * 4 <= self.ctx.ll_floats
+        algo = self.algo
+        if algo == ALGO_NVLS and not nvls_ok:
+            raise RuntimeError("B200RNN_ALGO=3 (NVLS) needs a multicast-capable symmetric region and a heap-resident arena")
+        if algo == ALGO_LL and not ll_fits:
+            raise RuntimeError(f"B200RNN_ALGO=4 (LL): {n} floats exceed the LL inbox ({self.ctx.ll_floats})")
+        if algo == ALGO_TWOSHOT and not in_heap:
+            algo = ALGO_AUTO
+        if algo != ALGO_AUTO:
+            return algo
+        if self.world == 1 or (ll_fits and nbytes <= t["ll_max_bytes"]):
+            return ALGO_LL
+        if nvls_ok and nbytes >= t["nvls_min_bytes"]:
+            return ALGO_NVLS
+        if in_heap and nbytes > t["oneshot_max_bytes"]:
+            return ALGO_TWOSHOT
+        return ALGO_ONESHOT
+
     def allreduce_update(self, rows: torch.Tensor, n_rows: int, arena, opt, optdesc, metrics_slot: torch.Tensor) -> None:
         self._seq_ar += 1
         heap_off = getattr(arena, "heap_off", None)
-        algo = self.algo if heap_off is not None else 1
         nvls_ok = self.mc_base is not None and heap_off is not None and hasattr(arena, "grad_heap_off")
-        if n_rows > 1 and heap_off is not None and self._picks_bulk(algo, arena.numel, nvls_ok):
-            # the bulk algorithms stream 4 elements per thread: reduce the per-CTA rows first with the
-            # 1-element-per-thread kernel (one extra launch) instead of serialising it inside them
+        algo = self.pick_algo(arena.numel, heap_off is not None, nvls_ok)
+        self.last_algo = algo
+        if n_rows > 1 and algo != ALGO_LL:
+            # only the LL form reduces the per-CTA rows itself; the streaming forms take one row
             _native.check(self.lib.b200rnn_reduce_rows(rows.data_ptr(), n_rows, arena.numel + 2, arena.grad.data_ptr(), 0,
                                                        self._sp()), "reduce_rows")
             _native.count_launch()
             rows, n_rows = arena.grad, 1
-        if algo == 3 and not nvls_ok:
-            raise RuntimeError("B200RNN_ALGO=3 (NVLS) needs a multicast-capable symmetric region")
-        if nvls_ok and (algo == 3 or (algo == 0 and arena.numel * 4 > self.NVLS_MIN_BYTES)):
+        if algo == ALGO_NVLS:
             _native.check(self.lib.b200rnn_comm_allreduce_update_nvls(
                 C.byref(self.ctx), self.mc_base, self._seq_ar, rows.data_ptr(), n_rows, arena.numel, arena.flat.data_ptr(),
                 heap_off, arena.grad_heap_off, opt.exp_avg.data_ptr(), opt.exp_avg_sq.data_ptr(), C.byref(optdesc),
                 metrics_slot.data_ptr(), self._sp()), "comm_allreduce_update_nvls")
             return
-        if algo == 3:
-            algo = 0
         _native.check(self.lib.b200rnn_comm_allreduce_update(
             C.byref(self.ctx), self._seq_ar, rows.data_ptr(), n_rows, arena.numel, arena.flat.data_ptr(),
             heap_off if heap_off is not None else -1, opt.exp_avg.data_ptr(), opt.exp_avg_sq.data_ptr(),
             C.byref(optdesc), metrics_slot.data_ptr(), algo, self._sp()), "comm_allreduce_update")
 
-    def _picks_bulk(self, algo: int, n: int, nvls_ok: bool) -> bool:
-        if algo in (2, 3):
-            return True
-        return algo == 0 and self.world > 1 and n * 4 * self.world > 128 * 1024   # mirrors the native auto rule
-
-    def allreduce_flat(self, t: torch.Tensor, average: bool = True) -> torch.Tensor:
+    def allreduce_flat(self, t: torch.Tensor, average: bool = True, algo: int = ALGO_AUTO) -> torch.Tensor:
         assert t.dtype == torch.float32 and t.is_contiguous()
         n, cap = t.numel(), self.ctx.inbox_floats
         scale = 1.0 / self.world if average else 1.0
         for lo in range(0, n, cap):
             k = min(cap, n - lo)
             self._seq_ar += 1
-            _native.check(self.lib.b200rnn_comm_allreduce(C.byref(self.ctx), self._seq_ar, t.data_ptr() + 4 * lo, k,
-                                                          scale, self._sp()), "comm_allreduce")
+            a = algo
+            if a == ALGO_AUTO:
+                ll_ok = (k + 3) // 4 * 4 <= self.ctx.ll_floats and k * 4 <= self.table["ll_max_bytes"]
+                a = ALGO_LL if ll_ok else ALGO_ONESHOT
+            _native.check(self.lib.b200rnn_comm_allreduce_algo(C.byref(self.ctx), self._seq_ar, t.data_ptr() + 4 * lo, k,
+                                                               scale, a, self._sp()), "comm_allreduce")
         _native.count_launch((n + cap - 1) // cap)
         return t
 

@@ -160,18 +160,17 @@ class Trainer:
                     self._save_checkpoint(epoch, validation_loss, best=True)
             if self.save_every and (epoch + 1) % self.save_every == 0:
                 self._save_checkpoint(epoch, training_history[-1], best=False)
+            # a fired watchdog (stuck peer, lost CTA) means this epoch trained on garbage: stop now, not after
+            # the last epoch; then keep the ranks together after rank-0-only work (validation, checkpoints)
+            self._health_check()
+            self._epoch_barrier()
         if cuda:
             ev1.record()
             torch.cuda.synchronize(self.device)
             self.last_device_seconds = ev0.elapsed_time(ev1) / 1e3
         duration = time.perf_counter() - start
         self.last_duration = duration
-        comm = self._get_comm()
-        if comm is not None and hasattr(comm, "check"):
-            comm.check()   # surface a fired comm watchdog (dead / stuck peer) instead of training on garbage
-        if cuda:
-            from .. import _native
-            _native.assert_device_healthy()   # same for the kernels' own bounded waits (TMA / MMA / wavefront)
+        self._health_check()
         logging.info(formatter.performance_message(peak_rss_mib(), duration))
         if cuda:
             logging.info("Rank: {:02d}   Device time: {:.6f} s, peak device memory: {:.1f} MiB".format(
@@ -179,6 +178,19 @@ class Trainer:
         if self.test_set is not None:
             self._evaluate(self.test_set, formatter)
         return self.model.eval(), training_history, validation_history
+
+    def _health_check(self) -> None:
+        """Raise if an in-kernel watchdog fired: the comm kernels' flag waits (dead / stuck peer) or the compute
+        kernels' own bounded waits (TMA / MMA / layer wavefront).  One small D2H read each."""
+        comm = self._get_comm()
+        if comm is not None and hasattr(comm, "check"):
+            comm.check()
+        if self.device.type == "cuda":
+            from .. import _native
+            _native.assert_device_healthy()
+
+    def _epoch_barrier(self) -> None:
+        """Hook: distributed trainers wait here for rank 0's validation / checkpoint of this epoch."""
 
     def _epoch_batches(self):
         idx = self.sampler.indices() if hasattr(self.sampler, "indices") else torch.tensor(list(iter(self.sampler)))
@@ -270,7 +282,7 @@ class Trainer:
 
     def load_checkpoint(self, path) -> dict:
         """Extension (the reference has no resume path): accepts prefixed and un-prefixed keys."""
-        ck = torch.load(path, map_location="cpu", weights_only=False)
+        ck = torch.load(path, map_location="cpu", weights_only=True)   # tensors + plain containers only
         state = ck["model_state"]
         own = self.model.state_dict()
         if any(k.startswith("module.") for k in state) and not any(k.startswith("module.") for k in own):

@@ -18,6 +18,8 @@ class DistributedTrainer(Trainer):
         self.rank, self.world_size = int(rank), int(world_size)
         shard = ShardedEpochSampler(len(training_set), num_replicas=self.world_size, rank=self.rank)
         eval_sets = dict(validation_set=validation_set, test_set=test_set) if self.is_root else {}
+        # rank 0 alone validates / checkpoints after an epoch; every rank knows whether it will
+        self._root_only_work = validation_set is not None or bool(trainer_kwargs.get("save_every"))
         super().__init__(model=model, training_set=training_set, batch_size=batch_size,
                          learning_rate=learning_rate, sampler=shard, **eval_sets, **trainer_kwargs)
 
@@ -31,6 +33,18 @@ class DistributedTrainer(Trainer):
 
     def _get_formatter(self, epochs):
         return TrainingMessageFormatter(epochs, self.rank)
+
+    def _epoch_barrier(self) -> None:
+        # Host-side barrier: without it the other ranks run ahead into the next epoch's first all-reduce and
+        # spin there (against the in-kernel watchdog) for as long as rank 0's evaluation / file write takes.
+        if not self._root_only_work or self.world_size == 1:
+            return
+        import torch
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            if self.device.type == "cuda":
+                torch.cuda.synchronize(self.device)
+            dist.barrier()
 
     def _save_checkpoint(self, epoch, loss, best=False):
         if not self.is_root:

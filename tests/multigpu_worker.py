@@ -38,11 +38,17 @@ def main():
         want = base.double() * sum(r + 1 for r in range(world))
         ok &= bool(torch.allclose(t.cpu().double(), want, rtol=1e-5, atol=1e-5))
         ok &= all(torch.equal(x, t) for x in gather_all(t))
+    for algo in (4, 1):     # both one-shot forms explicitly on the reference's gradient size
+        base = torch.randn(14150, generator=torch.Generator().manual_seed(algo))
+        t = (base * (rank + 1)).to(dev)
+        comm.allreduce_flat(t, average=False, algo=algo)
+        ok &= bool(torch.allclose(t.cpu().double(), base.double() * sum(r + 1 for r in range(world)), rtol=1e-5, atol=1e-5))
+        ok &= all(torch.equal(x, t) for x in gather_all(t))
     res["allreduce_ok"] = ok
 
     # 2. fused all-reduce + Adam (one-shot and two-shot) vs torch Adam on the averaged gradient
     res["nvls_available"] = comm.mc_base is not None
-    algos = [(1, "oneshot"), (2, "twoshot")] + ([(3, "nvls")] if comm.mc_base is not None else [])
+    algos = [(1, "oneshot"), (2, "twoshot"), (4, "ll")] + ([(3, "nvls")] if comm.mc_base is not None else [])
     for algo, name in algos:
         torch.manual_seed(5)
         lin = torch.nn.Linear(301, 97).to(dev)      # 29 294 parameters: several blocks, ragged tail

@@ -34,7 +34,7 @@ def test_topology_probe():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("algo", [1, 2])
+@pytest.mark.parametrize("algo", [1, 2, 4])
 def test_world1_allreduce_update_equals_fused_update(comm1, algo):
     torch.manual_seed(0)
     lin = torch.nn.Linear(129, 65).cuda()
@@ -70,6 +70,34 @@ def test_world1_allreduce_broadcast_barrier(comm1):
     comm1.broadcast_flat(v, root=0)
     comm1.check()
     assert torch.equal(v, w)
+    for n in (1, 3, 130, 14150, 65536):   # the LL form (auto for small vectors) and the flag form, ragged tails
+        for algo in (4, 1):
+            a = torch.randn(n, device="cuda")
+            b = a.clone()
+            comm1.allreduce_flat(a, average=False, algo=algo)
+            assert torch.equal(a, b), (n, algo)
+    comm1.check()
+
+
+@pytest.mark.gpu
+@pytest.mark.multigpu
+def test_watchdog_trips_instead_of_hanging():
+    """A rank that never joins an all-reduce: the others' in-kernel waits time out (B200RNN_COMM_TIMEOUT_MS),
+    check() raises on them, they exit non-zero, and nobody hangs."""
+    import os
+    import time
+    from pytorch_distributed_rnn_b200.parallel.launch import launch
+    n = min(torch.cuda.device_count(), 8)
+    env = dict(os.environ, B200RNN_COMM_TIMEOUT_MS="300")
+    t0 = time.time()
+    res = launch([sys.executable, str(ROOT / "tests" / "watchdog_worker.py")], n, timeout=240, env=env, fail_fast=False)
+    assert time.time() - t0 < 200
+    for r, cp in enumerate(res):
+        if r == n - 1:      # the rank that skipped the collective
+            assert cp.returncode == 0, (r, cp.stderr[-2000:])
+        else:
+            assert cp.returncode == 3, (r, cp.returncode, cp.stdout[-2000:], cp.stderr[-2000:])
+            assert "WATCHDOG_TRIPPED" in cp.stdout and f"rank(s) [{n - 1}]" in cp.stdout, cp.stdout[-2000:]
 
 
 @pytest.mark.gpu

@@ -94,6 +94,41 @@ def test_engine_train_steps_match_torch_adam(B, T, L):
     assert float(sd["state"][0]["step"]) == steps and sd["state"][0]["exp_avg"].shape == (128, 9)
 
 
+@pytest.mark.parametrize("B,T,L,cell", [(180, 24, 2, "lstm"), (720, 8, 2, "lstm"), (90, 12, 3, "lstm"), (1440, 6, 2, "lstm"),
+                                        (180, 16, 2, "gru")])
+def test_engine_index_slices_and_wavefront_handover(B, T, L, cell):
+    """The training-loop form of the step: batches are index slices of a device-resident dataset (read by the
+    kernels' own loaders, no gather launch), and from the second step on no sentinel fill is launched because
+    the backward put the sentinels back — 3 launches per step — with an evaluation in between (which leaves
+    activations in the stash, so the step after it must fill again).  Oracle: torch fp32 + torch.optim.Adam."""
+    torch.manual_seed(B + L)
+    steps, lr, N = 5, 0.0025, 2 * B + 7
+    model = MotionModel(9, 32, L, 6, cell=cell)
+    ref = copy.deepcopy(model)
+    feats, labels = torch.randn(N, T, 9), torch.randint(0, 6, (N, 1))
+    idxs = [torch.randperm(N)[:B] for _ in range(steps)]
+    want = _ref_train(ref, [feats[i] for i in idxs], [labels[i].view(-1) for i in idxs], lr, steps)
+    model = model.to(DEV)
+    eng = FusedTrainEngine(model, lr=lr)
+    fd, ld = feats.to(DEV), labels.to(DEV)
+    got, launches = [], []
+    for s in range(steps):
+        n0 = _native.launches()
+        m = eng.train_step_gather(fd, ld, idxs[s].to(DEV)).cpu()
+        launches.append(_native.launches() - n0)
+        got.append((float(m[0]) / B, int(round(float(m[1])))))
+        if s == 2:
+            eng.evaluate(fd[:B].contiguous(), ld[:B].contiguous())
+    _native.assert_device_healthy()
+    for (gl, gc), (wl, wc) in zip(got, want):
+        assert abs(gl - wl) < 2e-5, (got, want)
+        assert abs(gc - wc) <= max(1, B // 500), (got, want)
+    for (n, p), q in zip(model.named_parameters(), ref.parameters()):
+        assert torch.allclose(p.detach().cpu(), q.detach(), atol=5e-5), (n, float((p.detach().cpu() - q).abs().max()))
+    assert launches[1] == 3 and launches[2] == 3 and launches[4] == 3, launches
+    assert launches[0] >= 3 and launches[3] >= 3, launches
+
+
 def test_engine_evaluate_and_head():
     torch.manual_seed(0)
     model = MotionModel(9, 32, 2, 6)
