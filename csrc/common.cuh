@@ -56,6 +56,15 @@ __device__ __forceinline__ float tanh_f(float x) {
   return __fdividef(e - 1.0f, e + 1.0f);
 }
 
+// Packed fp32 FMA (FFMA2 in SASS, new with sm_100): acc.{x,y} += a.{x,y} * b.{x,y} in ONE issue slot.  A plain
+// three-register FFMA issues every other cycle per SM sub-partition on Blackwell, so a CUDA-core GEMV only
+// reaches the fp32 peak through the packed form; operands are natural register pairs (adjacent K elements).
+__device__ __forceinline__ void ffma2(float2& acc, const float2& a, const float2& b) {
+  asm("fma.rn.f32x2 %0, %1, %2, %0;"
+      : "+l"(reinterpret_cast<unsigned long long&>(acc))
+      : "l"(reinterpret_cast<const unsigned long long&>(a)), "l"(reinterpret_cast<const unsigned long long&>(b)));
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
