@@ -114,7 +114,7 @@ def run(n_gpus, steps, warmup, rank, world, device, cfg):
     torch.manual_seed(cfg["seed"])
     # synthetic data of the reference's shape (same generator as the own arm, plain torch)
     g = torch.Generator().manual_seed(0)
-    n = 6912
+    n = cfg.get("train_size", 6912)
     y = torch.randint(0, cfg["classes"], (n, 1), generator=g)
     x = torch.randn(n, cfg["seq_len"], cfg["features"], generator=g)
     train = MotionDataset(x, y)
@@ -137,9 +137,17 @@ def run(n_gpus, steps, warmup, rank, world, device, cfg):
     counter = {"h2d": 0}
     base_loader, sampler = trainer.train_loader, trainer.sampler
 
+    import contextlib
+    # scaled config: the reference's loop under bf16 autocast (what a user of the reference would switch on for
+    # a bf16 run; the loop itself is untouched)
+    amp = (lambda: torch.autocast("cuda", dtype=torch.bfloat16)) if cfg.get("autocast_bf16") else contextlib.nullcontext
+    if cfg.get("autocast_bf16"):
+        path += " under torch.autocast(bfloat16)"
+
     def run_steps(k):
         trainer.train_loader = _DeviceLoader(base_loader, sampler, device, k, counter)
-        return trainer._train_step(formatter)  # the reference's own hot loop (trainer/base.py:103-130)
+        with amp():
+            return trainer._train_step(formatter)  # the reference's own hot loop (trainer/base.py:103-130)
 
     run_steps(max(warmup, 3))
     if world > 1:
@@ -159,7 +167,7 @@ def run(n_gpus, steps, warmup, rank, world, device, cfg):
     # one epoch through the reference's own Trainer.train(1) (trainer/base.py:65-101): the BASELINE.md metric
     trainer.train_loader = _EpochLoader(base_loader, device)
     ep = []
-    for _ in range(2):
+    for _ in range(2 if cfg.get("epoch", True) else 0):
         if world > 1:
             torch.distributed.barrier()
         torch.cuda.synchronize(device)
@@ -167,12 +175,14 @@ def run(n_gpus, steps, warmup, rank, world, device, cfg):
         trainer.train(1)
         torch.cuda.synchronize(device)
         ep.append(time.perf_counter() - te)
-    if world > 1:
+    if world > 1 and ep:
         t = torch.tensor(ep, dtype=torch.float64, device=device)
         torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
         ep = [float(v) for v in t.tolist()]
-    epoch = {"first_epoch_s": ep[0], "epoch_s": ep[1], "samples": n, "steps": len(base_loader),
-             "samples_per_s": n / ep[1], "api": "reference Trainer.train(1), wall clock, max over ranks"}
+    epoch = None
+    if ep:
+        epoch = {"first_epoch_s": ep[0], "epoch_s": ep[1], "samples": n, "steps": len(base_loader),
+                 "samples_per_s": n / ep[1], "api": "reference Trainer.train(1), wall clock, max over ranks"}
     return {"epoch": epoch,"device_s": e0.elapsed_time(e1) / 1e3, "wall_s": wall, "window": (t_a, t_b), "path": path,
             "h2d_bytes_per_step": counter["h2d"] * world, "d2h_bytes_per_step": 8 * world,
             "final_loss": None}

@@ -6,7 +6,13 @@ T=128, Linear 32->6, CrossEntropy, Adam lr 0.0025, fp32 — at GLOBAL batch 1440
 1440 // N, the reference's rule, src/motion/trainer/distributed.py:48-49 => strong scaling), on
 synthetic data of the reference's shape (6 912 x [128, 9]) with random-init weights.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl own|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl own|reference] [--config motion|scaled]
+
+``--config scaled`` is BASELINE.json's config 4: the same classifier scaled to LSTM 9->1024 x 2 layers, T=512,
+bf16 operands (fp32 master weights / accumulation / state), 64 samples per GPU (weak scaling: the persistent
+recurrent kernels hold up to 128 rows), data-parallel with per-layer gradient buckets overlapped with the
+backward pass (ops/layered_engine.py); its reference arm is the reference's own model and trainer under
+``torch.autocast(bfloat16)`` + NCCL DistributedDataParallel.
 
 N > 1 is launched by the driver under torchrun (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* env).
 Rank 0 prints ONE JSON line.  Two measurements per run:
@@ -48,6 +54,7 @@ os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 GLOBAL_BATCH, SEQ_LEN, FEATURES, HIDDEN, LAYERS, CLASSES, TRAIN_SIZE = 1440, 128, 9, 32, 2, 6, 6912
 LR, SEED = 0.0025, 123456789
+SCALED = dict(hidden=1024, layers=2, seq_len=512, per_gpu_batch=64, batches_per_epoch=8)
 # best published number of the reference at batch 1440: 6912 samples / 3.595 s on its unnamed fast
 # host (results_baseline_1.json results[0])
 BASELINE_SAMPLES_PER_S = 6912 / 3.595
@@ -273,6 +280,119 @@ def run_own(args):
         dist.destroy_process_group()
 
 
+def run_own_scaled(args):
+    """BASELINE.json config 4 (see the module docstring).  Same three measurements as the motion config."""
+    import torch
+    from pytorch_distributed_rnn_b200 import MotionModel, ParamArena, _native
+    from pytorch_distributed_rnn_b200.data.sampler import epoch_indices
+    from pytorch_distributed_rnn_b200.ops.layered_engine import LayeredTrainEngine
+
+    rank, world, dev = dist_setup(args.gpus)
+    lib = _native.lib()
+    H, L, T, per_rank = SCALED["hidden"], SCALED["layers"], SCALED["seq_len"], SCALED["per_gpu_batch"]
+    gb = per_rank * world
+    n_train = gb * SCALED["batches_per_epoch"]
+    torch.manual_seed(SEED)
+    model = MotionModel(FEATURES, H, L, CLASSES).to(dev)
+    comm, arena, comm_kind = None, None, "none"
+    if world > 1:
+        from pytorch_distributed_rnn_b200.parallel.comm import make_comm
+        comm = make_comm()
+        comm_kind = comm.kind
+        arena = comm.make_arena(model) if hasattr(comm, "make_arena") else ParamArena(model)
+        comm.broadcast_flat(arena.flat[:arena.numel], root=0)
+    engine = LayeredTrainEngine(model, lr=LR, arena=arena, comm=comm)
+    K, W = args.steps, args.warmup
+    g = torch.Generator().manual_seed(0)
+    y_all = torch.randint(0, CLASSES, (n_train, 1), generator=g)
+    x_all = torch.randn(n_train, T, FEATURES, generator=g)
+    feats, labels = x_all.to(dev), y_all.to(dev)
+    full = SCALED["batches_per_epoch"]
+
+    def step_indices(s):
+        e, j = divmod(s, full)
+        return epoch_indices(n_train, world, rank, e)[j * per_rank:(j + 1) * per_rank]
+
+    idx_dev = [step_indices(s).to(dev) for s in range(W + K)]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    sp = _native.stream_ptr(dev)
+    sampler = ClockSampler(dev.index or 0) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    for s in range(W):
+        engine.train_step_gather(feats, labels, idx_dev[s])
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    barrier_sync(world, dev)
+    launches0 = _native.launches()
+    t_a = time.time()
+    for s in range(K):
+        lib.b200rnn_l2_flush(flush.data_ptr(), flush.numel(), sp)
+        ev[s][0].record()
+        engine.train_step_gather(feats, labels, idx_dev[W + s])
+        ev[s][1].record()
+    barrier_sync(world, dev)
+    t_b = time.time()
+    launches = _native.launches() - launches0
+    dev_ms = max_over_ranks(sum(a.elapsed_time(b) for a, b in ev), world, dev)
+    last = engine.metrics[(engine.n_steps - 1) % engine.METRIC_RING].cpu()
+
+    ring = 4
+    y_flat = y_all.view(-1)
+    pin_x = [torch.empty(per_rank, T, FEATURES).pin_memory() for _ in range(ring)]
+    pin_y = [torch.empty(per_rank, dtype=torch.int64).pin_memory() for _ in range(ring)]
+    idx_host = [step_indices(s) for s in range(max(W, 3) + K)]
+
+    def host_batches(first, count):
+        for s in range(first, first + count):
+            k = s % ring
+            torch.index_select(x_all, 0, idx_host[s], out=pin_x[k])
+            torch.index_select(y_flat, 0, idx_host[s], out=pin_y[k])
+            yield pin_x[k], pin_y[k]
+
+    for _ in engine.train_steps_host(host_batches(0, max(W, 3))):
+        pass
+    barrier_sync(world, dev)
+    t_c = time.time()
+    t0 = time.perf_counter()
+    n_results = sum(1 for _ in engine.train_steps_host(host_batches(max(W, 3), K)))
+    assert n_results == K
+    barrier_sync(world, dev)
+    e2e_s = max_over_ranks(time.perf_counter() - t0, world, dev)
+    t_d = time.time()
+    clocks = None
+    if sampler:
+        sampler.stop()
+        clocks = sampler.summary([(t_a, t_b), (t_c, t_d)])
+    _native.assert_device_healthy()
+    if comm is not None and hasattr(comm, "check"):
+        comm.check()
+    assert engine.reducer_status() == 0, "a reducer trigger wait timed out"
+    if rank == 0:
+        value = gb * K / (dev_ms / 1e3)
+        out = {
+            "metric": "scaled_lstm_ddp_train_samples_per_sec", "value": value, "unit": "samples/s", "n_gpus": world,
+            "steps": K, "warmup": W, "ms_per_step": dev_ms / K, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "impl": "own",
+            "config": {"model": f"LSTM 9->{H} x{L} layers, T={T}, Linear {H}->6, CE, Adam lr 0.0025 (BASELINE.json config 4)",
+                       "global_batch": gb, "seq_len": T, "parallelism": f"dp{world}", "per_rank_batch": per_rank,
+                       "comm": comm_kind, "precision": "bf16 GEMM operands, fp32 master weights / accumulation / cell state",
+                       "buckets": [{"name": n, "bytes": 4 * (hi - lo)} for n, lo, hi in engine.buckets],
+                       "l2": "256 MiB L2 flush between timed steps, outside the CUDA-event brackets",
+                       "timing": "per-step CUDA events on the launching stream, summed, max over ranks"},
+            "e2e": {"value": gb * K / e2e_s, "unit": "samples/s", "ms_per_step": 1e3 * e2e_s / K,
+                    "h2d_bytes_per_step": world * (pin_x[0].numel() * 4 + pin_y[0].numel() * 8), "d2h_bytes_per_step": world * 8,
+                    "api": "LayeredTrainEngine.train_steps_host(host_batches) -> yields (loss, correct) per step",
+                    "inputs": "every step, inside the timed region: host-side batch assembly into pinned memory, H2D copy, D2H loss read"},
+            "gpu_launches": launches, "launches_per_step": launches / K, "clocks": clocks,
+            "final_loss": float(last[0]) / per_rank,
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        barrier_sync(world, dev)
+        dist.destroy_process_group()
+
+
 def run_own_epoch(world, rank, dev, comm, x_all, y_all):
     """Wall clock of one epoch (5 steps incl. the partial 1 152-sample batch) through Trainer.train(1): the public
     training entry point, dataset device-resident (uploaded by the trainer's constructor, outside the clock — the
@@ -319,9 +439,14 @@ def run_reference(args):
     sampler = ClockSampler(dev.index or 0) if rank == 0 else None
     if sampler:
         sampler.start()
-    res = ref_adapter.run(args.gpus, args.steps, args.warmup, rank, world, dev,
-                          dict(global_batch=GLOBAL_BATCH, seq_len=SEQ_LEN, features=FEATURES, hidden=HIDDEN,
-                               layers=LAYERS, classes=CLASSES, lr=LR, seed=SEED))
+    scaled = args.config == "scaled"
+    gb = SCALED["per_gpu_batch"] * world if scaled else GLOBAL_BATCH
+    cfg = dict(global_batch=gb, seq_len=SEQ_LEN, features=FEATURES, hidden=HIDDEN, layers=LAYERS, classes=CLASSES,
+               lr=LR, seed=SEED, train_size=TRAIN_SIZE, autocast_bf16=False, epoch=True)
+    if scaled:
+        cfg.update(seq_len=SCALED["seq_len"], hidden=SCALED["hidden"], layers=SCALED["layers"],
+                   train_size=gb * SCALED["batches_per_epoch"], autocast_bf16=True, epoch=False)
+    res = ref_adapter.run(args.gpus, args.steps, args.warmup, rank, world, dev, cfg)
     clocks = None
     if sampler:
         sampler.stop()
@@ -330,17 +455,20 @@ def run_reference(args):
     wall_s = max_over_ranks(res["wall_s"], world, dev)
     if rank == 0:
         K = args.steps
-        value = GLOBAL_BATCH * K / dev_s
+        value = gb * K / dev_s
         out = {
-            "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": K, "warmup": args.warmup,
-            "ms_per_step": 1e3 * dev_s / K, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": value / BASELINE_SAMPLES_PER_S, "dtype": "fp32", "data": "synthetic", "impl": "reference",
-            "config": {"model": "reference MotionModel (nn.LSTM 9->32 x2, T=128, Linear 32->6), CE, Adam lr 0.0025",
-                       "global_batch": GLOBAL_BATCH, "seq_len": SEQ_LEN, "parallelism": f"dp{world}",
-                       "per_rank_batch": GLOBAL_BATCH // world,
+            "metric": "scaled_lstm_ddp_train_samples_per_sec" if scaled else METRIC, "value": value, "unit": "samples/s",
+            "n_gpus": world, "steps": K, "warmup": args.warmup,
+            "ms_per_step": 1e3 * dev_s / K, "higher_is_better": True, "scaling": "weak" if scaled else "strong",
+            "vs_baseline": None if scaled else value / BASELINE_SAMPLES_PER_S, "dtype": "bf16" if scaled else "fp32",
+            "data": "synthetic", "impl": "reference",
+            "config": {"model": f"reference MotionModel (nn.LSTM 9->{cfg['hidden']} x{cfg['layers']}, T={cfg['seq_len']}, "
+                                f"Linear {cfg['hidden']}->6), CE, Adam lr 0.0025" + (", torch.autocast(bfloat16)" if scaled else ""),
+                       "global_batch": gb, "seq_len": cfg["seq_len"], "parallelism": f"dp{world}",
+                       "per_rank_batch": gb // world,
                        "path": res["path"],
                        "timing": "CUDA events around the reference's own _train_step loop (K steps), max over ranks"},
-            "e2e": {"value": GLOBAL_BATCH * K / wall_s, "unit": "samples/s", "ms_per_step": 1e3 * wall_s / K,
+            "e2e": {"value": gb * K / wall_s, "unit": "samples/s", "ms_per_step": 1e3 * wall_s / K,
                     "h2d_bytes_per_step": res["h2d_bytes_per_step"], "d2h_bytes_per_step": res["d2h_bytes_per_step"]},
             "epoch": res.get("epoch"),
             "gpu_launches": None,
@@ -374,7 +502,10 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--config", default="motion", choices=["motion", "scaled"])
     args = ap.parse_args()
+    if args.config == "scaled" and "--steps" not in sys.argv:
+        args.steps, args.warmup = 10, 3   # ~25 ms per step
     if args.warmup < 3:
         args.warmup = 3  # timing rule: at least 3 warm-up steps
     import torch
@@ -383,6 +514,8 @@ def main():
         return
     if args.impl == "reference":
         run_reference(args)
+    elif args.config == "scaled":
+        run_own_scaled(args)
     else:
         run_own(args)
 

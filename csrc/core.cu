@@ -37,6 +37,19 @@ __global__ void gather_kernel(const float* __restrict__ feats, const int64_t* __
   if (threadIdx.x == 0 && labels != nullptr && y_out != nullptr) y_out[b] = labels[src];
 }
 
+// K11, time-major form: x_out[t][b][:] = feats[idx[b]][t][:] — the large-hidden path reads its input time-major
+// (one GEMM over all timesteps), so the gather and the [B,T,I] -> [T,B,I] transpose are one pass.
+__global__ void gather_tm_kernel(const float* __restrict__ feats, const int64_t* __restrict__ idx, int batch, int T, int I,
+                                 float* __restrict__ x_out) {
+  const int b = blockIdx.x;
+  const int64_t src = idx != nullptr ? idx[b] : (int64_t)b;
+  const float* s = feats + src * (int64_t)T * I;
+  for (int e = threadIdx.x; e < T * I; e += blockDim.x) {
+    const int t = e / I, i = e - t * I;
+    x_out[((int64_t)t * batch + b) * I + i] = __ldg(&s[e]);
+  }
+}
+
 // ---- deterministic row reduction ----
 __global__ void reduce_rows_kernel(const float* __restrict__ rows, int n_rows, int64_t row_floats,
                                    float* __restrict__ out, int accumulate) {
@@ -72,6 +85,24 @@ __global__ void __launch_bounds__(kRowThreads) fused_update_kernel(
       continue;
     }
     const float g = acc[e] * o.grad_scale;
+    if (grad_out != nullptr) grad_out[i] = g;
+    float p = params[i];
+    float m = exp_avg ? exp_avg[i] : 0.0f;
+    float v = exp_avg_sq ? exp_avg_sq[i] : 0.0f;
+    apply_update(o, g, p, m, v);
+    params[i] = p;
+    if (exp_avg) exp_avg[i] = m;
+    if (exp_avg_sq) exp_avg_sq[i] = v;
+  }
+}
+
+// Single gradient row (e.g. one bucket of an arena whose gradient came from GEMMs): plain streaming update, no
+// shared memory, so it co-resides with any compute kernel when it runs on a side stream.
+__global__ void __launch_bounds__(256) update_vec_kernel(
+    const float* __restrict__ g_in, int64_t n, float* __restrict__ params, float* __restrict__ exp_avg,
+    float* __restrict__ exp_avg_sq, OptScalars o, float* __restrict__ grad_out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float g = g_in[i] * o.grad_scale;
     if (grad_out != nullptr) grad_out[i] = g;
     float p = params[i];
     float m = exp_avg ? exp_avg[i] : 0.0f;
@@ -161,6 +192,15 @@ extern "C" int b200rnn_gather_batch(const float* feats, const int64_t* labels, c
   return B200RNN_OK;
 }
 
+extern "C" int b200rnn_gather_batch_tm(const float* feats, const int64_t* idx, int32_t batch, int32_t seq_len,
+                                       int32_t features, float* x_tm_out, void* stream) {
+  B200_REQUIRE(feats && x_tm_out && batch >= 0 && seq_len > 0 && features > 0, B200RNN_EINVAL, "gather_batch_tm: bad argument");
+  if (batch == 0) return B200RNN_OK;
+  gather_tm_kernel<<<batch, 256, 0, (cudaStream_t)stream>>>(feats, idx, batch, seq_len, features, x_tm_out);
+  B200_CHECK_LAUNCH();
+  return B200RNN_OK;
+}
+
 extern "C" int b200rnn_reduce_rows(const float* rows, int32_t n_rows, int64_t row_floats, float* out,
                                    int32_t accumulate, void* stream) {
   B200_REQUIRE(rows && out && n_rows >= 0 && row_floats > 0, B200RNN_EINVAL, "reduce_rows: bad argument");
@@ -181,6 +221,13 @@ extern "C" int b200rnn_fused_update(const float* rows, int32_t n_rows, int64_t n
   B200_REQUIRE(!(opt->kind == 1 && opt->momentum != 0.0f && !exp_avg), B200RNN_EINVAL,
                "fused_update: SGD momentum needs a momentum buffer (exp_avg)");
   const OptScalars o = make_opt_scalars(opt);
+  if (n_rows == 1 && metrics == nullptr) {
+    int64_t vb = (n_params + 255) / 256;
+    if (vb > 8 * num_sms()) vb = 8 * num_sms();
+    update_vec_kernel<<<(unsigned)vb, 256, 0, (cudaStream_t)stream>>>(rows, n_params, params, exp_avg, exp_avg_sq, o, grad_out);
+    B200_CHECK_LAUNCH();
+    return B200RNN_OK;
+  }
   const int64_t blocks = (n_params + 2 + kRowElems - 1) / kRowElems;
   if (rows_vectorizable(rows, n_params + 2))
     fused_update_kernel<true><<<(unsigned)blocks, kRowThreads, 0, (cudaStream_t)stream>>>(

@@ -42,7 +42,7 @@ template <int BN>
 __global__ void __launch_bounds__(256, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  void* __restrict__ Cout, const float* __restrict__ bias, int M, int N, int K, int ldc,
-                 int accumulate, int c_bf16) {
+                 int accumulate, int c_bf16, unsigned int* __restrict__ retire) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* sA = smem;
@@ -145,9 +145,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       }
     }
   }
+  if (retire != nullptr) __threadfence();   // this tile's stores are visible device-wide before it is counted
   tc_fence_before_sync();
   __syncthreads();
   if (warp == 2) tmem_dealloc<TM_COLS>(tmem_base);
+  // Tile retired: one release-add per CTA on the caller's counter.  A consumer kernel on another stream
+  // (the gradient bucket's all-reduce) spins on it and starts the moment the LAST tile of the weight-gradient
+  // GEMMs is out — the device-side "grad ready" trigger of the reducer (csrc/runtime/reducer.cpp).
+  if (retire != nullptr && threadIdx.x == 0)
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(retire) : "memory");
 }
 
 // fp32 -> bf16 cast, optionally transposing [R, C] -> [C, R] (operands of the dW GEMMs)
@@ -205,9 +211,19 @@ int make_map(CUtensorMap* map, const void* ptr, int rows, int k, int ld, int box
 
 using namespace b200rnn;
 
+extern "C" int b200rnn_gemm_bf16_retire(const void* A, const void* B, void* C, const float* bias, int32_t M, int32_t N,
+                                        int32_t K, int32_t lda, int32_t ldb, int32_t ldc, int32_t accumulate,
+                                        int32_t c_is_bf16, uint32_t* retire_counter, int32_t* retire_count, void* stream);
+
 extern "C" int b200rnn_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int32_t M, int32_t N,
                                  int32_t K, int32_t lda, int32_t ldb, int32_t ldc, int32_t accumulate,
                                  int32_t c_is_bf16, void* stream) {
+  return b200rnn_gemm_bf16_retire(A, B, C, bias, M, N, K, lda, ldb, ldc, accumulate, c_is_bf16, nullptr, nullptr, stream);
+}
+
+extern "C" int b200rnn_gemm_bf16_retire(const void* A, const void* B, void* C, const float* bias, int32_t M, int32_t N,
+                                        int32_t K, int32_t lda, int32_t ldb, int32_t ldc, int32_t accumulate,
+                                        int32_t c_is_bf16, uint32_t* retire_counter, int32_t* retire_count, void* stream) {
   B200_REQUIRE(A && B && C && M > 0 && N > 0 && K > 0, B200RNN_EINVAL, "gemm_bf16: bad argument");
   const bool skinny = (M <= BM) && ((N + 127) / 128 < num_sms() / 2) && N >= 32;
   const int64_t ctas256 = (int64_t)((N + 255) / 256) * ((M + BM - 1) / BM);
@@ -226,9 +242,11 @@ extern "C" int b200rnn_gemm_bf16(const void* A, const void* B, void* C, const fl
     attr_set = true;
   }
   dim3 grid((N + bn - 1) / bn, (M + BM - 1) / BM);
-  if (skinny) gemm_bf16_kernel<32><<<grid, 256, smem_bytes<32>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16);
-  else if (wide) gemm_bf16_kernel<256><<<grid, 256, smem_bytes<256>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16);
-  else gemm_bf16_kernel<128><<<grid, 256, smem_bytes<128>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16);
+  if (retire_count) *retire_count = (int32_t)(grid.x * grid.y);   // increments this launch adds to retire_counter
+  unsigned int* rc_ptr = retire_counter;
+  if (skinny) gemm_bf16_kernel<32><<<grid, 256, smem_bytes<32>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16, rc_ptr);
+  else if (wide) gemm_bf16_kernel<256><<<grid, 256, smem_bytes<256>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16, rc_ptr);
+  else gemm_bf16_kernel<128><<<grid, 256, smem_bytes<128>(), (cudaStream_t)stream>>>(ma, mb, C, bias, M, N, K, ldc, accumulate, c_is_bf16, rc_ptr);
   B200_CHECK_LAUNCH();
   return B200RNN_OK;
 }

@@ -19,6 +19,8 @@
 
 extern "C" int b200rnn_gemm_bf16(const void*, const void*, void*, const float*, int32_t, int32_t, int32_t, int32_t,
                                  int32_t, int32_t, int32_t, int32_t, void*);
+extern "C" int b200rnn_gemm_bf16_retire(const void*, const void*, void*, const float*, int32_t, int32_t, int32_t, int32_t,
+                                        int32_t, int32_t, int32_t, int32_t, uint32_t*, int32_t*, void*);
 extern "C" int b200rnn_transpose_cast_bf16(const float*, void*, int32_t, int32_t, int64_t, int64_t, void*);
 // persistent time loops (rnn_persist.cu)
 extern "C" int b200rnn_rnn_persist_supported(const b200rnn_model_desc*);
@@ -143,12 +145,22 @@ __global__ void colsum_partial(const float* __restrict__ in, int64_t rows, int c
     part[(int64_t)blockIdx.y * cols + c] = t;
   }
 }
-__global__ void colsum_final(const float* __restrict__ part, int slabs, int cols, float* __restrict__ out) {
+// out2 (nullable): second destination of the same sums (LSTM: db_hh == db_ih).  retire (nullable): counted once
+// per block after its stores, like the GEMM tiles (see gemm_tc.cu).
+__global__ void colsum_final(const float* __restrict__ part, int slabs, int cols, float* __restrict__ out,
+                             float* __restrict__ out2, unsigned int* __restrict__ retire) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
-  float acc = 0.0f;
-  for (int s = 0; s < slabs; ++s) acc += part[(int64_t)s * cols + c];
-  out[c] = acc;
+  if (c < cols) {
+    float acc = 0.0f;
+    for (int s = 0; s < slabs; ++s) acc += part[(int64_t)s * cols + c];
+    out[c] = acc;
+    if (out2 != nullptr) out2[c] = acc;
+  }
+  if (retire != nullptr) {
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(retire) : "memory");
+  }
 }
 // fp32 [rows, cols] -> bf16 [rows, ld_out] (zero padded columns)
 __global__ void cast_pad_bf16(const float* __restrict__ in, int64_t rows, int cols, int64_t ld_in, bf16* __restrict__ out, int ld_out) {
@@ -173,11 +185,13 @@ inline int grid_for(int64_t n, int threads = 256, int cap = 2368) {
 inline int pad8(int x) { return (x + 7) & ~7; }
 // tmp must hold colsum_slabs(rows) * cols floats
 inline int colsum_slabs(int64_t rows) { int64_t s = rows / 8; return (int)(s < 1 ? 1 : (s > 64 ? 64 : s)); }
-inline void colsum(const float* in, int64_t rows, int cols, float* out, float* tmp, cudaStream_t st) {
+inline int colsum(const float* in, int64_t rows, int cols, float* out, float* tmp, cudaStream_t st,
+                  float* out2 = nullptr, unsigned int* retire = nullptr) {
   const int slabs = colsum_slabs(rows);
   const int64_t slab = (rows + slabs - 1) / slabs;
   colsum_partial<<<dim3((cols + 31) / 32, slabs), dim3(32, 8), 0, st>>>(in, rows, cols, slab, tmp);
-  colsum_final<<<(cols + 127) / 128, 128, 0, st>>>(tmp, slabs, cols, out);
+  colsum_final<<<(cols + 127) / 128, 128, 0, st>>>(tmp, slabs, cols, out, out2, retire);
+  return (cols + 127) / 128;   // blocks that will count themselves on `retire`
 }
 
 #define RC(x) do { int _rc = (x); if (_rc != B200RNN_OK) return _rc; } while (0)
@@ -357,27 +371,29 @@ extern "C" int b200rnn_rnn_large_fwd(const b200rnn_model_desc* d, const float* p
   return B200RNN_OK;
 }
 
-// Backward through time.  d_out_tm: gradient of the top layer's output sequence, time-major [T,B,H]
-// (nullable); d_hn / d_cn: [L,B,H] (nullable).  grad_out: flat gradient in parameter layout
-// (d->n_params floats, fully overwritten for the RNN parameters).  dx_tm: [T,B,I] (nullable).
-extern "C" int b200rnn_rnn_large_bwd(const b200rnn_model_desc* d, const float* params, const float* x_tm, const void* stash,
-                                     void* scratch, const float* d_out_tm, const float* d_hn, const float* d_cn,
-                                     float* grad_out, float* dx_tm, void* stream) {
-  B200_REQUIRE(d && params && x_tm && stash && scratch && grad_out, B200RNN_EINVAL, "rnn_large_bwd: null argument");
+// Backward through time of ONE layer (the body of b200rnn_rnn_large_bwd).  Gradients of this layer's four
+// parameter tensors are complete when the call's kernels have run; every kernel that writes one of them (the two
+// weight-gradient GEMMs tile by tile, the bias column sums block by block) counts itself on `retire` (nullable)
+// as it finishes, and *retire_count receives how many such counts this call will add — the reducer's trigger
+// for the layer's gradient bucket (csrc/runtime/reducer.cpp; c10d's per-bucket "grad ready" hooks fire at
+// the same point, src/motion/trainer/ddp.py:19).
+static int large_bwd_layer(const b200rnn_model_desc* d, const float* params, const float* x_tm, const void* stash,
+                           const Scratch& sc, int l, const float* d_out_tm, const float* d_hn, const float* d_cn,
+                           float* grad_out, float* dx_tm, unsigned int* retire, int32_t* retire_count, void* stream) {
   const int H = d->hidden_size, B = d->batch, T = d->seq_len, L = d->num_layers;
   const bool lstm = d->cell == B200RNN_CELL_LSTM;
   const int G = lstm ? 4 : 3;
   const int64_t TB = (int64_t)T * B, Bh = (int64_t)B * H;
   const int64_t TBp = (TB + 7) & ~int64_t(7);
   cudaStream_t s = (cudaStream_t)stream;
-  const Scratch sc = carve(d, scratch);
+  int32_t counted = 0, n = 0;
   // layer offsets inside the stash
   int64_t loff[B200RNN_MAX_LAYERS];
   {
     int64_t o = 0;
-    for (int l = 0; l < L; ++l) { loff[l] = o; o += layer_layout(d->cell, l == 0 ? d->input_size : H, H, TB).total; }
+    for (int k = 0; k < L; ++k) { loff[k] = o; o += layer_layout(d->cell, k == 0 ? d->input_size : H, H, TB).total; }
   }
-  for (int l = L - 1; l >= 0; --l) {
+  {
     const int in_l = l == 0 ? d->input_size : H;
     const LargeLayout lay = layer_layout(d->cell, in_l, H, TB);
     const char* st = (const char*)stash + loff[l];
@@ -433,22 +449,53 @@ extern "C" int b200rnn_rnn_large_bwd(const b200rnn_model_desc* d, const float* p
     RC(b200rnn_transpose_cast_bf16(sc.dG, sc.dGT_b, (int32_t)TB, G * H, G * H, TBp, stream));
     B200_CHECK_CUDA(cudaMemsetAsync(sc.xT_b, 0, (size_t)pad8(in_l > H ? in_l : H) * TBp * 2, s));
     RC(b200rnn_transpose_cast_bf16(xin, sc.xT_b, (int32_t)TB, in_l, in_l, TBp, stream));
-    RC(b200rnn_gemm_bf16(sc.dGT_b, sc.xT_b, grad_out + d->off_wih[l], nullptr, G * H, in_l, (int32_t)TBp, (int32_t)TBp,
-                         (int32_t)TBp, in_l, 0, 0, stream));
+    RC(b200rnn_gemm_bf16_retire(sc.dGT_b, sc.xT_b, grad_out + d->off_wih[l], nullptr, G * H, in_l, (int32_t)TBp, (int32_t)TBp,
+                                (int32_t)TBp, in_l, 0, 0, retire, &n, stream));
+    counted += n;
     if (!lstm) {
       B200_CHECK_CUDA(cudaMemsetAsync(sc.dGT_b, 0, (size_t)G * H * TBp * 2, s));
       RC(b200rnn_transpose_cast_bf16(sc.dG2, sc.dGT_b, (int32_t)TB, G * H, G * H, TBp, stream));
     }
     B200_CHECK_CUDA(cudaMemsetAsync(sc.xT_b, 0, (size_t)pad8(in_l > H ? in_l : H) * TBp * 2, s));
     if (T > 1) RC(b200rnn_transpose_cast_bf16(h, sc.xT_b + B, (int32_t)(TB - B), H, H, TBp, stream));   // H_prev = h shifted by one step
-    RC(b200rnn_gemm_bf16(sc.dGT_b, sc.xT_b, grad_out + d->off_whh[l], nullptr, G * H, H, (int32_t)TBp, (int32_t)TBp,
-                         (int32_t)TBp, H, 0, 0, stream));
+    RC(b200rnn_gemm_bf16_retire(sc.dGT_b, sc.xT_b, grad_out + d->off_whh[l], nullptr, G * H, H, (int32_t)TBp, (int32_t)TBp,
+                                (int32_t)TBp, H, 0, 0, retire, &n, stream));
+    counted += n;
     // biases
     // sc.dX (TB x pad8(inmax) floats >= slabs x G*H) is free here and serves as the partial-sum buffer
-    colsum(sc.dG, TB, G * H, grad_out + d->off_bih[l], sc.dX, s);
-    if (lstm) B200_CHECK_CUDA(cudaMemcpyAsync(grad_out + d->off_bhh[l], grad_out + d->off_bih[l], (size_t)G * H * 4, cudaMemcpyDeviceToDevice, s));
-    else colsum(sc.dG2, TB, G * H, grad_out + d->off_bhh[l], sc.dX, s);
+    if (lstm) counted += colsum(sc.dG, TB, G * H, grad_out + d->off_bih[l], sc.dX, s, grad_out + d->off_bhh[l], retire);
+    else {
+      counted += colsum(sc.dG, TB, G * H, grad_out + d->off_bih[l], sc.dX, s, nullptr, retire);
+      counted += colsum(sc.dG2, TB, G * H, grad_out + d->off_bhh[l], sc.dX, s, nullptr, retire);
+    }
     B200_CHECK_LAUNCH();
   }
+  if (retire_count) *retire_count = counted;
   return B200RNN_OK;
+}
+
+// Backward through time.  d_out_tm: gradient of the top layer's output sequence, time-major [T,B,H]
+// (nullable); d_hn / d_cn: [L,B,H] (nullable).  grad_out: flat gradient in parameter layout
+// (d->n_params floats, fully overwritten for the RNN parameters).  dx_tm: [T,B,I] (nullable).
+extern "C" int b200rnn_rnn_large_bwd(const b200rnn_model_desc* d, const float* params, const float* x_tm, const void* stash,
+                                     void* scratch, const float* d_out_tm, const float* d_hn, const float* d_cn,
+                                     float* grad_out, float* dx_tm, void* stream) {
+  B200_REQUIRE(d && params && x_tm && stash && scratch && grad_out, B200RNN_EINVAL, "rnn_large_bwd: null argument");
+  const Scratch sc = carve(d, scratch);
+  for (int l = d->num_layers - 1; l >= 0; --l)
+    RC(large_bwd_layer(d, params, x_tm, stash, sc, l, d_out_tm, d_hn, d_cn, grad_out, dx_tm, nullptr, nullptr, stream));
+  return B200RNN_OK;
+}
+
+// One layer of the above (call for layer = L-1 down to 0 on the same stash / scratch: the gradient that flows
+// to the layer below is kept in the scratch between calls).  See large_bwd_layer for retire / retire_count.
+extern "C" int b200rnn_rnn_large_bwd_layer(const b200rnn_model_desc* d, const float* params, const float* x_tm,
+                                           const void* stash, void* scratch, int32_t layer, const float* d_out_tm,
+                                           const float* d_hn, const float* d_cn, float* grad_out, float* dx_tm,
+                                           uint32_t* retire_counter, int32_t* retire_count, void* stream) {
+  B200_REQUIRE(d && params && x_tm && stash && scratch && grad_out && layer >= 0 && layer < d->num_layers, B200RNN_EINVAL,
+               "rnn_large_bwd_layer: bad argument");
+  const Scratch sc = carve(d, scratch);
+  return large_bwd_layer(d, params, x_tm, stash, sc, layer, d_out_tm, d_hn, d_cn, grad_out, dx_tm, retire_counter,
+                         retire_count, stream);
 }

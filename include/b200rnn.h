@@ -65,6 +65,10 @@ int b200rnn_version(void);
 int b200rnn_gather_batch(const float* feats, const int64_t* labels,
                          const int64_t* idx, int32_t batch, int32_t row_elems,
                          float* x_out, int64_t* y_out, void* stream);
+/* Time-major form for the large-hidden path: x_tm_out[t][b][:] = feats[idx[b]][t][:] (idx nullable = identity),
+ * i.e. gather and [B,T,I] -> [T,B,I] transpose in one pass. */
+int b200rnn_gather_batch_tm(const float* feats, const int64_t* idx, int32_t batch, int32_t seq_len,
+                            int32_t features, float* x_tm_out, void* stream);
 
 /* ---- K2/K3: fused persistent recurrent kernels, small-hidden family
  * (whole sequence, all layers, one launch; recurrent weights register-resident).
@@ -205,6 +209,22 @@ int b200rnn_head_fwd(const float* h_last, int64_t ld_h, const float* fc_w, const
                      const int64_t* labels, int32_t batch, int32_t hidden, int32_t classes,
                      float* logits, float* metrics, void* stream);
 
+/* K5 with its backward: head + mean cross-entropy + correct count + all their gradients in two launches
+ * (csrc/head/head_ce.cu) — what models outside the small-hidden fused family use instead of nn.Linear +
+ * CrossEntropyLoss + argmax and their autograd backward (src/motion/model.py:16, trainer/base.py:112-116).
+ * labels[idx ? idx[b] : b] (idx nullable); loss scaled by loss_scale (normally 1/B) for the gradients.
+ * Outputs: d_h [B,H] (row stride ld_dh) = gradient of h_last, d_w [C,H], d_b [C], metrics[2] = (sum of
+ * per-sample losses, correct count).  scratch: b200rnn_head_ce_scratch_floats(B, C) floats.  Every block of
+ * the weight-gradient kernel adds one count to retire_counter (nullable) when done; *retire_count (nullable)
+ * receives how many.  b200rnn_head_status: bit 0 = a label outside [0, C) was met (treated as class 0). */
+int64_t b200rnn_head_ce_scratch_floats(int32_t batch, int32_t classes);
+int b200rnn_head_ce(const float* h_last, int64_t ld_h, const float* fc_w, const float* fc_b,
+                    const int64_t* labels, const int64_t* idx, int32_t batch, int32_t hidden,
+                    int32_t classes, float loss_scale, float* d_h, int64_t ld_dh, float* d_w,
+                    float* d_b, float* metrics, float* scratch, uint32_t* retire_counter,
+                    int32_t* retire_count, void* stream);
+int b200rnn_head_status(int32_t* status);
+
 /* ---- K6: fused optimizers on the flat arena (src/motion/trainer/base.py:42-43,117;
  * src/example/example_ddp.py:54,82). */
 typedef struct {
@@ -231,6 +251,13 @@ int b200rnn_fused_update(const float* rows, int32_t n_rows, int64_t n_params,
 int b200rnn_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int32_t M, int32_t N,
                       int32_t K, int32_t lda, int32_t ldb, int32_t ldc, int32_t accumulate,
                       int32_t c_is_bf16, void* stream);
+/* Same GEMM whose CTAs each add one count (red.release.gpu) to *retire_counter once their output tile is
+ * stored; *retire_count receives the number of tiles.  The reducer's wait kernel (b200rnn_reducer_wait) on
+ * another stream starts the gradient bucket's all-reduce when the last tile of the weight-gradient GEMMs has
+ * retired (K4 -> K7 trigger; c10d fires its bucket hooks at the same point, src/motion/trainer/ddp.py:19). */
+int b200rnn_gemm_bf16_retire(const void* A, const void* B, void* C, const float* bias, int32_t M, int32_t N,
+                             int32_t K, int32_t lda, int32_t ldb, int32_t ldc, int32_t accumulate,
+                             int32_t c_is_bf16, uint32_t* retire_counter, int32_t* retire_count, void* stream);
 /* 0 = no tensor-core pipeline timeout has been observed since the library was loaded. */
 int b200rnn_gemm_status(int32_t* status);
 /* fp32 -> bf16 cast; and cast + transpose [rows, cols] -> [cols, rows]. */
@@ -256,6 +283,15 @@ int b200rnn_rnn_large_fwd(const b200rnn_model_desc* d, const float* params, cons
 int b200rnn_rnn_large_bwd(const b200rnn_model_desc* d, const float* params, const float* x_tm,
                           const void* stash, void* scratch, const float* d_out_tm, const float* d_hn,
                           const float* d_cn, float* grad_out, float* dx_tm, void* stream);
+
+/* One layer of b200rnn_rnn_large_bwd: call for layer = L-1 down to 0 on the same stash / scratch (the gradient
+ * flowing to the layer below stays in the scratch between calls).  When the call's kernels have run, the
+ * gradients of this layer's four parameter tensors are complete; every kernel that writes one of them counts
+ * itself on retire_counter (nullable) and *retire_count (nullable) receives how many counts will be added. */
+int b200rnn_rnn_large_bwd_layer(const b200rnn_model_desc* d, const float* params, const float* x_tm,
+                                const void* stash, void* scratch, int32_t layer, const float* d_out_tm,
+                                const float* d_hn, const float* d_cn, float* grad_out, float* dx_tm,
+                                uint32_t* retire_counter, int32_t* retire_count, void* stream);
 
 /* Persistent time loops of the large-hidden LSTM (csrc/rnn/rnn_persist.cu): one cooperative launch
  * per layer and direction, W_hh sharded across the SMs' shared memory, h_t / dG_t exchanged through
@@ -341,11 +377,30 @@ int b200rnn_symm_vmm_create(b200rnn_boot* b, int32_t rank, int32_t world, int32_
 int b200rnn_symm_vmm_pointers(b200rnn_symm_vmm* s, void** out /* [world] */, void** mc_out);
 int b200rnn_symm_vmm_destroy(b200rnn_symm_vmm* s);
 
-/* ---- N7 reducer: bucket assignment in reverse parameter order (c10d policy: 1 MiB first
- * bucket, then `cap`).  bucket_of[i] = bucket index of parameter i (bucket 0 holds the LAST
- * parameters, whose gradients are ready first). ---- */
+/* ---- N7 reducer (csrc/runtime/reducer.cpp).
+ * Bucket assignment in reverse parameter order (c10d policy: 1 MiB first bucket, then `cap`):
+ * bucket_of[i] = bucket index of parameter i (bucket 0 holds the LAST parameters, whose gradients are
+ * ready first). */
 int b200rnn_bucket_plan(const int64_t* sizes_bytes, int32_t n, int64_t first_cap, int64_t cap,
                         int32_t* bucket_of, int32_t* n_buckets);
+/* Device-side "bucket ready" triggers.  A bucket is the arena slice [lo, hi) (floats).  Producers — the
+ * kernels that write the bucket's gradient — count themselves on b200rnn_reducer_counter(r, bucket) as they
+ * retire; the host promises how many counts a step adds (b200rnn_reducer_expect) and enqueues
+ * b200rnn_reducer_wait on the communication stream in front of the bucket's all-reduce: a one-thread kernel
+ * that spins until the promised counts have arrived (bounded; b200rnn_reducer_read reports a timeout as
+ * bit `bucket` of the status word) and stamps %globaltimer.  b200rnn_reducer_stamp enqueues a kernel that
+ * writes %globaltimer into mark `which` (1..3) of the bucket — e.g. "collective done", "next layer's
+ * backward begins / ends" — so the overlap can be read back as a timeline (stamps_out[bucket][0..3], ns).
+ * b200rnn_reducer_create ALLOCATES a few hundred bytes of device memory. */
+typedef struct b200rnn_reducer b200rnn_reducer;
+int b200rnn_reducer_create(int32_t n_buckets, const int64_t* lo, const int64_t* hi, b200rnn_reducer** out);
+int b200rnn_reducer_destroy(b200rnn_reducer* r);
+int b200rnn_reducer_range(const b200rnn_reducer* r, int32_t bucket, int64_t* lo, int64_t* hi);
+uint32_t* b200rnn_reducer_counter(b200rnn_reducer* r, int32_t bucket);
+int b200rnn_reducer_expect(b200rnn_reducer* r, int32_t bucket, int32_t counts);
+int b200rnn_reducer_wait(b200rnn_reducer* r, int32_t bucket, void* stream);
+int b200rnn_reducer_stamp(b200rnn_reducer* r, int32_t bucket, int32_t which, void* stream);
+int b200rnn_reducer_read(b200rnn_reducer* r, uint64_t* stamps_out, int32_t* status_out);
 
 /* ---- Communicator context handed (by value) to every comm kernel. ---- */
 typedef struct {

@@ -129,6 +129,20 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_symm_vmm_pointers": (i32, [vp, P(vp), P(vp)]),
         "b200rnn_symm_vmm_destroy": (i32, [vp]),
         "b200rnn_bucket_plan": (i32, [P(i64), i32, i64, i64, P(i32), P(i32)]),
+        "b200rnn_reducer_create": (i32, [i32, P(i64), P(i64), P(vp)]),
+        "b200rnn_reducer_destroy": (i32, [vp]),
+        "b200rnn_reducer_range": (i32, [vp, i32, P(i64), P(i64)]),
+        "b200rnn_reducer_counter": (vp, [vp, i32]),
+        "b200rnn_reducer_expect": (i32, [vp, i32, i32]),
+        "b200rnn_reducer_wait": (i32, [vp, i32, vp]),
+        "b200rnn_reducer_stamp": (i32, [vp, i32, i32, vp]),
+        "b200rnn_reducer_read": (i32, [vp, P(C.c_uint64), P(i32)]),
+        "b200rnn_head_ce_scratch_floats": (i64, [i32, i32]),
+        "b200rnn_head_ce": (i32, [vp, i64, vp, vp, vp, vp, i32, i32, i32, f32, vp, i64, vp, vp, vp, vp, vp, P(i32), vp]),
+        "b200rnn_head_status": (i32, [P(i32)]),
+        "b200rnn_gather_batch_tm": (i32, [vp, vp, i32, i32, i32, vp, vp]),
+        "b200rnn_gemm_bf16_retire": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp, P(i32), vp]),
+        "b200rnn_rnn_large_bwd_layer": (i32, [P(ModelDesc), vp, vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, P(i32), vp]),
         # in-kernel collectives
         "b200rnn_comm_layout": (i64, [P(CommCtx)]),
         "b200rnn_comm_allreduce_update": (i32, [P(CommCtx), C.c_uint32, vp, i32, i64, vp, i64, vp, vp, P(OptimDesc), vp, i32, vp]),
@@ -186,7 +200,7 @@ def device_status() -> dict:
     pipeline, the persistent large-hidden time loops and the small-hidden layer wavefront.  All zero = healthy."""
     out = {}
     l = lib()
-    for name in ("gemm", "persist", "wave", "tc"):
+    for name in ("gemm", "persist", "wave", "tc", "head"):
         fn = getattr(l, f"b200rnn_{name}_status", None)
         if fn is None:
             continue
@@ -199,7 +213,7 @@ def device_status() -> dict:
 def assert_device_healthy() -> None:
     """Raise if any in-kernel watchdog fired since the library was loaded (results of that call are garbage)."""
     bad = {k: v for k, v in device_status().items() if v != 0}
-    if bad.get("wave", 0) & 2:
+    if bad.get("wave", 0) & 2 or bad.get("head", 0) & 1:
         raise NativeError("fused head: a label outside [0, num_classes) reached the loss (status %r)" % (bad,))
     if bad:
         raise NativeError(f"in-kernel watchdog fired: {bad} (a wait for a peer CTA / TMA / MMA timed out; "

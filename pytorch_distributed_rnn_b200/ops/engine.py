@@ -35,7 +35,89 @@ from .optim import FusedAdam, _FlatOptimizer
 from .rnn_function import CELL_ID
 
 
-class FusedTrainEngine:
+class HostStepsMixin:
+    """End-to-end stepping from HOST batches for an engine that provides ``train_step(x_dev, y_dev)``, ``device``,
+    ``_copy_stream`` and ``_host_metrics`` (shared by the small-hidden and the layered large-hidden engines)."""
+
+    def train_step_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> Tuple[float, int]:
+        """End-to-end step from host memory: H2D copy of the batch (pass pinned tensors for an async
+        DMA), the 3-launch training step, and a D2H read of this step's result.
+        Returns (mean cross-entropy loss of the batch, correct count)."""
+        B = x_host.shape[0]
+        stage = getattr(self, "_host_stage", None)
+        if stage is None or stage[0].shape != x_host.shape:
+            stage = (torch.empty(x_host.shape, dtype=torch.float32, device=self.device),
+                     torch.empty(B, dtype=torch.int64, device=self.device))
+            self._host_stage = stage
+        if self._host_metrics is None:
+            self._host_metrics = torch.zeros(2, dtype=torch.float32).pin_memory()
+        stage[0].copy_(x_host, non_blocking=True)
+        stage[1].copy_(y_host.reshape(-1), non_blocking=True)
+        m = self.train_step(stage[0], stage[1])
+        self._host_metrics.copy_(m, non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        return float(self._host_metrics[0]) / B, int(round(float(self._host_metrics[1])))
+
+    def train_steps_host(self, batches):
+        """Pipelined end-to-end training over an iterable of HOST batches ``(x, y)`` (pinned memory for
+        truly asynchronous DMA).  Generator: yields ``(mean loss, correct count)`` for every step, in
+        order.  Each step still copies ITS inputs host->device and has ITS result read back
+        device->host, but the copy of step s+1 runs on a side stream while step s computes, and the
+        result of step s is read while step s+1 is already queued (one-step lag), so neither PCIe
+        transfer sits on the critical path."""
+        dev = self.device
+        main = torch.cuda.current_stream(dev)
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(dev)
+        cs = self._copy_stream
+        slots = [None, None]          # double-buffered device batches
+        copied = [torch.cuda.Event(), torch.cuda.Event()]
+        consumed = [torch.cuda.Event(), torch.cuda.Event()]
+        results = [torch.zeros(2, dtype=torch.float32).pin_memory() for _ in range(2)]
+        res_ready = [torch.cuda.Event(), torch.cuda.Event()]
+
+        def stage(i, x, y):
+            if slots[i] is None or slots[i][0].shape != x.shape:
+                slots[i] = (torch.empty(x.shape, dtype=torch.float32, device=dev),
+                            torch.empty(y.numel(), dtype=torch.int64, device=dev))
+            with torch.cuda.stream(cs):
+                cs.wait_event(consumed[i])            # the step that last used this slot has finished
+                slots[i][0].copy_(x, non_blocking=True)
+                slots[i][1].copy_(y.reshape(-1), non_blocking=True)
+                copied[i].record(cs)
+
+        it = iter(batches)
+        nxt = next(it, None)
+        if nxt is None:
+            return
+        for e in consumed:
+            e.record(main)
+        stage(0, *nxt)
+        s = 0
+        pending = None                                # (slot, batch size) of the step whose result is in flight
+        while nxt is not None:
+            i = s & 1
+            cur_B = nxt[0].shape[0]
+            nxt = next(it, None)
+            if nxt is not None:
+                stage(i ^ 1, *nxt)                    # prefetch the next batch while this one computes
+            main.wait_event(copied[i])
+            m = self.train_step(slots[i][0], slots[i][1])
+            consumed[i].record(main)
+            results[i].copy_(m, non_blocking=True)
+            res_ready[i].record(main)
+            if pending is not None:
+                j, Bj = pending
+                res_ready[j].synchronize()
+                yield float(results[j][0]) / Bj, int(round(float(results[j][1])))
+            pending = (i, cur_B)
+            s += 1
+        j, Bj = pending
+        res_ready[j].synchronize()
+        yield float(results[j][0]) / Bj, int(round(float(results[j][1])))
+
+
+class FusedTrainEngine(HostStepsMixin):
     METRIC_RING = 1024
 
     def __init__(self, model: MotionModel, optimizer: Optional[_FlatOptimizer] = None, lr: float = 0.0025,
@@ -189,82 +271,6 @@ class FusedTrainEngine:
         """Train on rows ``idx`` of a device-resident dataset (feats [N,T,I], labels [N] or [N,1]): the gather of
         the reference's DataLoader (src/motion/trainer/base.py:107) happens inside the forward / backward loaders."""
         return self.train_step(feats, labels, idx)
-
-    def train_step_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> Tuple[float, int]:
-        """End-to-end step from host memory: H2D copy of the batch (pass pinned tensors for an async
-        DMA), the 3-launch training step, and a D2H read of this step's result.
-        Returns (mean cross-entropy loss of the batch, correct count)."""
-        B, T, I = x_host.shape
-        buf = self._get(B, T)
-        if buf["x"] is None:
-            buf["x"] = torch.empty(B, T, I, dtype=torch.float32, device=self.device)
-            buf["y"] = torch.empty(B, dtype=torch.int64, device=self.device)
-        if self._host_metrics is None:
-            self._host_metrics = torch.zeros(2, dtype=torch.float32).pin_memory()
-        buf["x"].copy_(x_host, non_blocking=True)
-        buf["y"].copy_(y_host.reshape(-1), non_blocking=True)
-        m = self.train_step(buf["x"], buf["y"])
-        self._host_metrics.copy_(m, non_blocking=True)
-        torch.cuda.current_stream(self.device).synchronize()
-        return float(self._host_metrics[0]) / B, int(round(float(self._host_metrics[1])))
-
-    def train_steps_host(self, batches):
-        """Pipelined end-to-end training over an iterable of HOST batches ``(x, y)`` (pinned memory for
-        truly asynchronous DMA).  Generator: yields ``(mean loss, correct count)`` for every step, in
-        order.  Each step still copies ITS inputs host->device and has ITS result read back
-        device->host, but the copy of step s+1 runs on a side stream while step s computes, and the
-        result of step s is read while step s+1 is already queued (one-step lag), so neither PCIe
-        transfer sits on the critical path."""
-        dev = self.device
-        main = torch.cuda.current_stream(dev)
-        if self._copy_stream is None:
-            self._copy_stream = torch.cuda.Stream(dev)
-        cs = self._copy_stream
-        slots = [None, None]          # double-buffered device batches
-        copied = [torch.cuda.Event(), torch.cuda.Event()]
-        consumed = [torch.cuda.Event(), torch.cuda.Event()]
-        results = [torch.zeros(2, dtype=torch.float32).pin_memory() for _ in range(2)]
-        res_ready = [torch.cuda.Event(), torch.cuda.Event()]
-
-        def stage(i, x, y):
-            if slots[i] is None or slots[i][0].shape != x.shape:
-                slots[i] = (torch.empty(x.shape, dtype=torch.float32, device=dev),
-                            torch.empty(y.numel(), dtype=torch.int64, device=dev))
-            with torch.cuda.stream(cs):
-                cs.wait_event(consumed[i])            # the step that last used this slot has finished
-                slots[i][0].copy_(x, non_blocking=True)
-                slots[i][1].copy_(y.reshape(-1), non_blocking=True)
-                copied[i].record(cs)
-
-        it = iter(batches)
-        nxt = next(it, None)
-        if nxt is None:
-            return
-        for e in consumed:
-            e.record(main)
-        stage(0, *nxt)
-        s = 0
-        pending = None                                # (slot, batch size) of the step whose result is in flight
-        while nxt is not None:
-            i = s & 1
-            cur_B = nxt[0].shape[0]
-            nxt = next(it, None)
-            if nxt is not None:
-                stage(i ^ 1, *nxt)                    # prefetch the next batch while this one computes
-            main.wait_event(copied[i])
-            m = self.train_step(slots[i][0], slots[i][1])
-            consumed[i].record(main)
-            results[i].copy_(m, non_blocking=True)
-            res_ready[i].record(main)
-            if pending is not None:
-                j, Bj = pending
-                res_ready[j].synchronize()
-                yield float(results[j][0]) / Bj, int(round(float(results[j][1])))
-            pending = (i, cur_B)
-            s += 1
-        j, Bj = pending
-        res_ready[j].synchronize()
-        yield float(results[j][0]) / Bj, int(round(float(results[j][1])))
 
     @torch.no_grad()
     def evaluate(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:

@@ -240,6 +240,30 @@ class SymmComm:
             heap_off if heap_off is not None else -1, opt.exp_avg.data_ptr(), opt.exp_avg_sq.data_ptr(),
             C.byref(optdesc), metrics_slot.data_ptr(), algo, self._sp()), "comm_allreduce_update")
 
+    def allreduce_update_slice(self, arena, opt, optdesc, lo: int, hi: int) -> None:
+        """K7 on one gradient bucket: all-reduce ``arena.grad[lo:hi]`` (a single row), average, and run the
+        optimizer on ``arena.flat[lo:hi]`` and its state — on the CURRENT stream (the layered engine calls this on
+        its communication stream, behind the reducer's device-side trigger).  All ranks must call it for the same
+        buckets in the same order."""
+        self._seq_ar += 1
+        n = hi - lo
+        heap_off = getattr(arena, "heap_off", None)
+        in_heap = heap_off is not None and (heap_off + 4 * lo) % 16 == 0
+        nvls_ok = (self.mc_base is not None and in_heap and hasattr(arena, "grad_heap_off")
+                   and (arena.grad_heap_off + 4 * lo) % 16 == 0)
+        algo = self.pick_algo(n, in_heap, nvls_ok)
+        self.last_algo = algo
+        g = arena.grad.data_ptr() + 4 * lo
+        p, m, v = arena.flat.data_ptr() + 4 * lo, opt.exp_avg.data_ptr() + 4 * lo, opt.exp_avg_sq.data_ptr() + 4 * lo
+        if algo == ALGO_NVLS:
+            _native.check(self.lib.b200rnn_comm_allreduce_update_nvls(
+                C.byref(self.ctx), self.mc_base, self._seq_ar, g, 1, n, p, heap_off + 4 * lo, arena.grad_heap_off + 4 * lo,
+                m, v, C.byref(optdesc), None, self._sp()), "comm_allreduce_update_nvls")
+            return
+        _native.check(self.lib.b200rnn_comm_allreduce_update(
+            C.byref(self.ctx), self._seq_ar, g, 1, n, p, heap_off + 4 * lo if in_heap else -1, m, v, C.byref(optdesc), None,
+            algo, self._sp()), "comm_allreduce_update")
+
     def allreduce_flat(self, t: torch.Tensor, average: bool = True, algo: int = ALGO_AUTO) -> torch.Tensor:
         assert t.dtype == torch.float32 and t.is_contiguous()
         n, cap = t.numel(), self.ctx.inbox_floats

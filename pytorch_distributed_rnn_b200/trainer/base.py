@@ -120,8 +120,13 @@ class Trainer:
             return None
         try:
             return FusedTrainEngine(core, optimizer=self._flat_optimizer(), arena=self.arena, comm=self._get_comm())
+        except NotImplementedError:
+            pass
+        try:   # large-hidden family: tcgen05 GEMMs + persistent recurrence, per-layer gradient buckets
+            from ..ops.layered_engine import LayeredTrainEngine
+            return LayeredTrainEngine(core, optimizer=self._flat_optimizer(), arena=self.arena, comm=self._get_comm())
         except NotImplementedError as e:
-            logging.warning("fused engine unavailable for this shape (%s); using the composite torch path", e)
+            logging.warning("no fused engine for this shape (%s); using the composite torch path", e)
             return None
 
     def _flat_optimizer(self):

@@ -152,6 +152,36 @@ def main():
     res["ddp_overlap_ok"] = ov
     res["ddp_buckets"] = len(ddp.buckets)
 
+    # 4c. large-hidden engine: per-layer gradient buckets, device-side triggers, slice all-reduce + Adam on the
+    #     communication stream — against torch DistributedDataParallel (NCCL) on an fp32 twin of the model
+    from pytorch_distributed_rnn_b200.ops.layered_engine import LayeredTrainEngine
+    from torch.nn.parallel import DistributedDataParallel as TorchDDP
+    torch.manual_seed(77)
+    big = MotionModel(9, 128, 2, 6).to(dev)
+    twin = TorchDDP(copy.deepcopy(big), device_ids=[dev.index])
+    b_arena = comm.make_arena(big)
+    comm.broadcast_flat(b_arena.flat[:b_arena.numel], root=0)
+    leng = LayeredTrainEngine(big, lr=0.0025, arena=b_arena, comm=comm, timeline=True)
+    topt = torch.optim.Adam(twin.parameters(), lr=0.0025)
+    lay = True
+    for step in range(3):
+        g = torch.Generator().manual_seed(500 + 10 * step + rank)
+        xb, yb = torch.randn(16, 24, 9, generator=g).to(dev), torch.randint(0, 6, (16,), generator=g).to(dev)
+        mine = leng.train_step(xb, yb).clone()
+        topt.zero_grad()
+        tl = torch.nn.functional.cross_entropy(twin(xb), yb)
+        tl.backward()
+        topt.step()
+        lay &= abs(float(mine[0]) / 16 - float(tl)) < 2e-2 * max(1.0, abs(float(tl)))
+    torch.cuda.synchronize()
+    pd = torch.cat([(p.detach() - q.detach()).abs().view(-1) for p, q in zip(big.parameters(), twin.module.parameters())])
+    res["layered_param_mean_abs_diff"] = float(pd.mean())
+    lay &= float(pd.mean()) < 0.25 * 0.0025 * 3
+    lay &= all(torch.equal(x, b_arena.flat[:b_arena.numel].clone()) for x in gather_all(b_arena.flat[:b_arena.numel].clone()))
+    lay &= leng.reducer_status() == 0
+    res["layered_timeline"] = leng.last_timeline()
+    res["layered_ddp_ok"] = lay
+
     # 5. buffer-reuse soak with injected delay on one rank (straggler)
     comm.set_delay_ns(20000 if rank == world - 1 else 0)
     soak = True
