@@ -367,6 +367,12 @@ def run_own_scaled(args):
     if comm is not None and hasattr(comm, "check"):
         comm.check()
     assert engine.reducer_status() == 0, "a reducer trigger wait timed out"
+    # one more step, outside every timed region, with %globaltimer stamps: when each gradient bucket's trigger fired,
+    # when its collective / optimizer finished, and when each layer's backward began and ended
+    engine.timeline = True
+    engine.train_step_gather(feats, labels, idx_dev[-1])
+    timeline = engine.last_timeline()
+    engine.timeline = False
     if rank == 0:
         value = gb * K / (dev_ms / 1e3)
         out = {
@@ -384,6 +390,7 @@ def run_own_scaled(args):
                     "api": "LayeredTrainEngine.train_steps_host(host_batches) -> yields (loss, correct) per step",
                     "inputs": "every step, inside the timed region: host-side batch assembly into pinned memory, H2D copy, D2H loss read"},
             "gpu_launches": launches, "launches_per_step": launches / K, "clocks": clocks,
+            "overlap_timeline_us": timeline,
             "final_loss": float(last[0]) / per_rank,
         }
         print(json.dumps(out), flush=True)

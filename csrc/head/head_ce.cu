@@ -26,6 +26,7 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_ce_sample_kernel(
     float* __restrict__ part /* [grid][2] */, int* __restrict__ status) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = blockIdx.x * kWarpsPerBlock + warp;
+  __shared__ float dl_s[kWarpsPerBlock][32];
   float loss = 0.f, corr = 0.f;
   if (b < B) {
     const float* hb = h + (int64_t)b * ld_h;
@@ -56,10 +57,14 @@ __global__ void __launch_bounds__(kWarpsPerBlock * 32) head_ce_sample_kernel(
       const float dl = lane < C ? (expf(mine - lse) - (lane == y ? 1.f : 0.f)) * loss_scale : 0.f;
       if (dlogits != nullptr && lane < C) dlogits[(int64_t)b * C + lane] = dl;
       if (dh != nullptr) {
+        // dlogits of this sample through shared memory: the k loop below is ragged across lanes (H need not be a
+        // multiple of 32), so it must not contain warp-synchronous shuffles
+        dl_s[warp][lane] = dl;
+        __syncwarp();
         float* o = dh + (int64_t)b * ld_dh;
         for (int k = lane; k < H; k += 32) {
           float acc = 0.f;
-          for (int c = 0; c < C; ++c) acc = fmaf(__shfl_sync(0xffffffffu, dl, c), W[(int64_t)c * H + k], acc);
+          for (int c = 0; c < C; ++c) acc = fmaf(dl_s[warp][c], W[(int64_t)c * H + k], acc);
           o[k] = acc;
         }
       }

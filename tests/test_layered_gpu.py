@@ -33,8 +33,9 @@ def test_head_ce_kernels_match_torch(B, H, Cn):
     scratch = torch.empty(lib.b200rnn_head_ce_scratch_floats(B, Cn), device=DEV)
     counter = torch.zeros(1, dtype=torch.int32, device=DEV)
     cnt = C.c_int32(0)
-    _native.check(lib.b200rnn_head_ce(hd.data_ptr(), H, wd.data_ptr(), bd.data_ptr(), labels.to(DEV).data_ptr(),
-                                      idx.to(DEV).data_ptr(), B, H, Cn, 1.0 / B, d_h.data_ptr(), H, d_w.data_ptr(),
+    labels_d, idx_d = labels.to(DEV), idx.to(DEV)      # named: a temporary would be freed before the kernel reads it
+    _native.check(lib.b200rnn_head_ce(hd.data_ptr(), H, wd.data_ptr(), bd.data_ptr(), labels_d.data_ptr(),
+                                      idx_d.data_ptr(), B, H, Cn, 1.0 / B, d_h.data_ptr(), H, d_w.data_ptr(),
                                       d_b.data_ptr(), met.data_ptr(), scratch.data_ptr(), counter.data_ptr(), C.byref(cnt),
                                       _native.stream_ptr()), "head_ce")
     torch.cuda.synchronize()
