@@ -341,9 +341,19 @@ __global__ void __launch_bounds__(kThreads) twoshot_kernel(
     const long long lo = (long long)p * shard;
     const long long hi = lo + shard < n ? lo + shard : n;
     float* dst = inbox(c, p, seq, c.rank);
-    for (long long i = lo + t0; i < hi; i += tstride) {
-      const F4 g = UPDATE ? reduce_rows4(rows, n_rows, row_stride, i, hi) : reduce_rows4(buf, 1, 0, i, hi);
-      store4(dst - lo, g, i, hi);
+    constexpr int U = 4;   // independent 128-bit loads in flight per thread: the loop is latency-bound otherwise
+    for (long long i0 = lo + t0; i0 < hi; i0 += U * tstride) {
+      F4 g[U];
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        const long long i = i0 + k * tstride;
+        if (i < hi) g[k] = UPDATE ? reduce_rows4(rows, n_rows, row_stride, i, hi) : reduce_rows4(buf, 1, 0, i, hi);
+      }
+#pragma unroll
+      for (int k = 0; k < U; ++k) {
+        const long long i = i0 + k * tstride;
+        if (i < hi) store4(dst - lo, g[k], i, hi);
+      }
     }
   }
   grid_sync(c, counter, sync_target - gridDim.x);
@@ -357,32 +367,47 @@ __global__ void __launch_bounds__(kThreads) twoshot_kernel(
   {
     const long long lo = (long long)c.rank * shard;
     const long long hi = lo + shard < n ? lo + shard : n;
-    for (long long i = lo + t0; i < hi; i += tstride) {
-      F4 sum; sum.v[0] = sum.v[1] = sum.v[2] = sum.v[3] = 0.0f;
-      for (int s = 0; s < c.world; ++s) {
-        const F4 t = load4_cg(inbox(c, c.rank, seq, s) - lo, i, hi);
+    constexpr int U2 = 2;   // two elements per thread and iteration: 2 x W independent inbox loads in flight
+    for (long long i0 = lo + t0; i0 < hi; i0 += U2 * tstride) {
+      F4 sum[U2];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) sum.v[e] += t.v[e];
-      }
-      F4 out;
+      for (int k = 0; k < U2; ++k) sum[k].v[0] = sum[k].v[1] = sum[k].v[2] = sum[k].v[3] = 0.0f;
+#pragma unroll 4
+      for (int s = 0; s < c.world; ++s) {   // fixed rank order => identical bits on every rank
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const long long j = i + e;
-        float r = sum.v[e] * scale;
-        if (UPDATE && j < hi) {
-          float p = buf[j];
-          float m = exp_avg ? exp_avg[j] : 0.0f;
-          float v = exp_avg_sq ? exp_avg_sq[j] : 0.0f;
-          apply_update(o, sum.v[e] * o.grad_scale, p, m, v);
-          if (exp_avg) exp_avg[j] = m;
-          if (exp_avg_sq) exp_avg_sq[j] = v;
-          r = p;
+        for (int k = 0; k < U2; ++k) {
+          const long long i = i0 + k * tstride;
+          if (i < hi) {
+            const F4 t = load4_cg(inbox(c, c.rank, seq, s) - lo, i, hi);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) sum[k].v[e] += t.v[e];
+          }
         }
-        out.v[e] = r;
       }
-      for (int dp = 0; dp < c.world; ++dp) {   // all-gather by peer stores (self first)
-        const int p = (c.rank + dp) % c.world;
-        store4(reinterpret_cast<float*>(c.base[p] + c.off_heap + buf_heap_off), out, i, hi);
+#pragma unroll
+      for (int k = 0; k < U2; ++k) {
+        const long long i = i0 + k * tstride;
+        if (i >= hi) break;
+        F4 out;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const long long j = i + e;
+          float r = sum[k].v[e] * scale;
+          if (UPDATE && j < hi) {
+            float p = buf[j];
+            float m = exp_avg ? exp_avg[j] : 0.0f;
+            float v = exp_avg_sq ? exp_avg_sq[j] : 0.0f;
+            apply_update(o, sum[k].v[e] * o.grad_scale, p, m, v);
+            if (exp_avg) exp_avg[j] = m;
+            if (exp_avg_sq) exp_avg_sq[j] = v;
+            r = p;
+          }
+          out.v[e] = r;
+        }
+        for (int dp = 0; dp < c.world; ++dp) {   // all-gather by peer stores (self first)
+          const int p = (c.rank + dp) % c.world;
+          store4(reinterpret_cast<float*>(c.base[p] + c.off_heap + buf_heap_off), out, i, hi);
+        }
       }
     }
   }

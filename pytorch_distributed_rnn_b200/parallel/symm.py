@@ -108,7 +108,7 @@ class SymmComm:
         ctx.rank, ctx.world, ctx.max_blocks, ctx.delay_ns = self.rank, self.world, max_blocks, delay_ns
         # watchdog of the in-kernel waits: B200RNN_COMM_TIMEOUT_MS (default 60 s, resolved natively when 0 here)
         ctx.inbox_floats, ctx.timeout_cycles, ctx.heap_bytes = inbox_floats, 0, heap_bytes
-        ctx.ll_floats = int(os.environ.get("B200RNN_LL_FLOATS", 64 << 10))
+        ctx.ll_floats = int(os.environ.get("B200RNN_LL_FLOATS", 256 << 10))   # LL one-shot up to 1 MiB vectors
         region = self.lib.b200rnn_comm_layout(C.byref(ctx))
         if region <= 0:
             raise _native.NativeError("comm_layout failed")
