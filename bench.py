@@ -49,8 +49,17 @@ from pathlib import Path
 
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
-# stdout carries exactly ONE JSON line: send NCCL's own log lines (e.g. "NCCL version ...") to stderr
+# stdout carries exactly ONE JSON line.  Libraries write banners to file descriptor 1 behind Python's back (NCCL prints
+# "NCCL version ..." there), so fd 1 is pointed at stderr for the whole run and the JSON line goes to a duplicate of
+# the original stdout.
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+_REAL_STDOUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(obj) -> None:
+    _REAL_STDOUT.write(json.dumps(obj) + "\n")
+    _REAL_STDOUT.flush()
 
 GLOBAL_BATCH, SEQ_LEN, FEATURES, HIDDEN, LAYERS, CLASSES, TRAIN_SIZE = 1440, 128, 9, 32, 2, 6, 6912
 LR, SEED = 0.0025, 123456789
@@ -273,7 +282,7 @@ def run_own(args):
             "clocks": clocks,
             "final_loss": float(last[0]) / per_rank,
         }
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         import torch.distributed as dist
         barrier_sync(world, dev)
@@ -393,7 +402,7 @@ def run_own_scaled(args):
             "overlap_timeline_us": timeline,
             "final_loss": float(last[0]) / per_rank,
         }
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         import torch.distributed as dist
         barrier_sync(world, dev)
@@ -434,13 +443,13 @@ def run_reference(args):
     try:
         from baseline import ref_adapter
     except Exception as e:  # noqa: BLE001
-        print(json.dumps({"impl": "reference", "unavailable": f"adapter import failed: {type(e).__name__}: {e}"}), flush=True)
+        emit({"impl": "reference", "unavailable": f"adapter import failed: {type(e).__name__}: {e}"})
         return
     why = ref_adapter.unavailable_reason()
     if why:
         rank = int(os.environ.get("RANK", "0"))
         if rank == 0:
-            print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
+            emit({"impl": "reference", "unavailable": why})
         return
     rank, world, dev = dist_setup_reference(args.gpus)
     sampler = ClockSampler(dev.index or 0) if rank == 0 else None
@@ -482,7 +491,7 @@ def run_reference(args):
             "clocks": clocks,
             "final_loss": res.get("final_loss"),
         }
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
@@ -517,7 +526,7 @@ def main():
         args.warmup = 3  # timing rule: at least 3 warm-up steps
     import torch
     if not torch.cuda.is_available():
-        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device visible"}), flush=True)
+        emit({"impl": args.impl, "unavailable": "no CUDA device visible"})
         return
     if args.impl == "reference":
         run_reference(args)

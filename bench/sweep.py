@@ -13,6 +13,11 @@ created if missing (quirk Q15).  ``--network`` runs the delay-injection variant 
 ``distributed`` and ``horovod`` trainers at the largest rank count for each injected delay.
 
     python bench/sweep.py --dataset-path /tmp/motion --results results.json [--ranks 1,2,4,8] [--repeats 2]
+
+``--pack G`` (G = GPUs of the box) runs configurations that need fewer than G GPUs side by side on disjoint
+GPU sets (CUDA_VISIBLE_DEVICES), largest world first — the reference ran its grid on one cluster serially;
+here a run is a few seconds of start-up around a few milliseconds of training, so packing the box is what keeps
+the experiment affordable.  The recorded duration is each run's own in-process measurement either way.
 """
 from __future__ import annotations
 
@@ -79,6 +84,50 @@ def run_training(runs, dataset_path, results_file, env=None, tag=None):
             json.dump({"results": results}, f)
 
 
+def run_packed(runs, dataset_path, results_file, n_gpus, env=None, tag=None):
+    """Same bookkeeping as run_training, with runs of n ranks started n_gpus // n at a time on disjoint GPUs."""
+    import tempfile
+    import time
+    by_n = {}
+    for run in runs:
+        by_n.setdefault(run["hosts"] * run["slots"], []).append(run)
+    for n in sorted(by_n, reverse=True):
+        pending = list(by_n[n])
+        random.shuffle(pending)
+        free = [list(range(i * n, (i + 1) * n)) for i in range(max(1, n_gpus // n))]
+        active = []
+        while pending or active:
+            while pending and free:
+                run = pending.pop()
+                cmd = get_command(run, dataset_path)
+                command = " ".join(cmd) + (f"  #{tag}" if tag else "") + f"  #repeat{run.get('repeat', 0)}"
+                if any(r["command"] == command for r in load_results(results_file)):
+                    print(f"skip (already recorded): {command}")
+                    continue
+                gpus = free.pop()
+                e = dict(os.environ, PYTHONPATH=str(ROOT), CUDA_VISIBLE_DEVICES=",".join(map(str, gpus)))
+                e.update(env or {})
+                fo, fe = tempfile.TemporaryFile("w+"), tempfile.TemporaryFile("w+")
+                print(f"[n={n} gpus={gpus}] {command}", flush=True)
+                active.append((run, command, gpus, subprocess.Popen(cmd, stdout=fo, stderr=fe, env=e, cwd=str(ROOT)), fo, fe))
+            for item in list(active):
+                run, command, gpus, proc, fo, fe = item
+                if proc.poll() is None:
+                    continue
+                fo.seek(0); fe.seek(0)
+                entry = {"command": command, "stdout": fo.read(), "stderr": fe.read(), "returncode": proc.returncode,
+                         "config": {k: run[k] for k in ("trainer", "hosts", "slots", "parameters")}, "gpus": gpus}
+                if tag:
+                    entry.update(tag_fields(tag))
+                results = load_results(results_file)
+                results.append(entry)
+                with open(results_file, "w") as f:
+                    json.dump({"results": results}, f)
+                active.remove(item)
+                free.append(gpus)
+            time.sleep(0.1)
+
+
 def tag_fields(tag):
     kind, value = tag.split("=")
     return {"rule_type": kind, "rule_value": float(value), "rule": f"{kind} {value}us"}
@@ -91,13 +140,23 @@ def main():
     ap.add_argument("--ranks", default="1,2,4,8")
     ap.add_argument("--repeats", type=int, default=2)
     ap.add_argument("--network", action="store_true", help="delay-injection experiment instead of the scaling grid")
+    ap.add_argument("--pack", type=int, default=0, help="GPUs of the box: run smaller worlds side by side on disjoint GPUs")
+    ap.add_argument("--delays", default=",".join(map(str, DELAYS_US)), help="--network: injected delays in us")
     a = ap.parse_args()
     ranks = [int(x) for x in a.ranks.split(",")]
+    # one dataset for the whole experiment, written before anything runs (runs may start side by side)
+    sys.path.insert(0, str(ROOT))
+    from pytorch_distributed_rnn_b200.data import synthetic
+    if not synthetic.is_complete(a.dataset_path):
+        synthetic.write_dataset(a.dataset_path, seed=123456789)
     if not a.network:
-        run_training(train_runs(ranks, a.repeats), a.dataset_path, a.results)
+        if a.pack:
+            run_packed(train_runs(ranks, a.repeats), a.dataset_path, a.results, a.pack)
+        else:
+            run_training(train_runs(ranks, a.repeats), a.dataset_path, a.results)
         return
     n = max(ranks)
-    for d in DELAYS_US:
+    for d in [int(x) for x in a.delays.split(",")]:
         runs = [{"trainer": tr, "hosts": n, "slots": 1,
                  "parameters": {"--batch-size": 1440, "--epochs": 1, "--seed": 123456789, "--no-validation": ""}}
                 for tr in ("distributed", "horovod")]

@@ -21,6 +21,7 @@
 // for the 16-byte global stride rule).  Every mbarrier wait is bounded; a timeout sets an error
 // word that b200rnn_gemm_status() reports.
 #include <cuda_bf16.h>
+#include <cstdlib>
 #include "tc_common.cuh"
 
 namespace b200rnn {
@@ -156,6 +157,223 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(retire) : "memory");
 }
 
+
+// ---------------------------------------------------------------------------
+// Persistent form for the bulk GEMMs (input projection over all timesteps, dX, dW): one CTA per SM walks a
+// static list of 128x256 output tiles.  Two 256-column fp32 accumulators fill the SM's 512 TMEM columns, so
+// the epilogue of tile i (TMEM -> registers -> 128B-swizzled shared memory -> TMA store) runs while the MMA
+// warp is already accumulating tile i+1; the operand ring (4 stages x 48 KiB) never drains between tiles.
+//   warp 0   : TMA producer (A 128x64, B 256x64 bf16 boxes, 128B swizzle)
+//   warp 1   : MMA issuer (4 x tcgen05.mma M128 N256 K16 per stage), commits `empty[s]` per stage and
+//              `acc_full[a]` per tile; waits `acc_empty[a]` before reusing accumulator a
+//   warp 2   : TMEM allocator
+//   warps 4-7: epilogue, one TMEM lane quarter (32 output rows) each.  Per 128-byte column chunk (32 fp32 or
+//              64 bf16 columns): tcgen05.ld, + bias, swizzled st.shared, then ONE cp.async.bulk.tensor store
+//              (cp.reduce...add when accumulating) issued by an elected lane — `UTMASTG` / `UTMAREDG` in SASS.  Each warp owns two
+//              4 KiB staging slabs, so chunk c+1 is being assembled while chunk c drains.
+// Tiles are ordered M-fastest: CTAs that run concurrently share the B (weight) panel in L2.
+// ---------------------------------------------------------------------------
+namespace persist {
+constexpr int BN = 256, NACC = 2;
+constexpr int B_TILE = BN * BK * 2;                               // 32 KiB
+constexpr int RING = STAGES * (TILE_BYTES + B_TILE);              // 192 KiB
+constexpr int SLAB = 32 * 128;                                    // 32 rows x 128 bytes
+constexpr int STAGING = 4 * 2 * SLAB;                             // 4 warps x 2 slabs = 32 KiB
+constexpr int SMEM = RING + STAGING + 256 + 1024;
+}  // namespace persist
+
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem_src, int c0, int c1, bool add) {
+  if (add)
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+  else
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+template <bool C_BF16>
+__global__ void __launch_bounds__(256, 1)
+gemm_bf16_persist_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                         const __grid_constant__ CUtensorMap tma_c, const float* __restrict__ bias, int M, int N, int K,
+                         int accumulate, unsigned int* __restrict__ retire) {
+  using namespace persist;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STAGES * TILE_BYTES;
+  uint8_t* stage_base = smem + RING;                               // 1024-byte aligned (RING is a multiple of 1024)
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + RING + STAGING);
+  uint64_t* empty = full + STAGES;
+  uint64_t* acc_full = empty + STAGES;
+  uint64_t* acc_empty = acc_full + NACC;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + NACC);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nk = (K + BK - 1) / BK;
+  const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN;
+  const int n_tiles = tiles_m * tiles_n;
+
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&tma_a); tma_prefetch_desc(&tma_b); tma_prefetch_desc(&tma_c); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < NACC; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 4); }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<512>(tmem_slot);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer =====
+    int it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      const int m0 = (tile % tiles_m) * BM, n0 = (tile / tiles_m) * BN;
+      for (int kb = 0; kb < nk; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        if (!mbar_wait(&empty[s], ph ^ 1)) { atomicExch(&g_gemm_error, 1); return; }
+        mbar_expect_tx(&full[s], TILE_BYTES + B_TILE);
+        tma_load_2d(sA + s * TILE_BYTES, &tma_a, &full[s], kb * BK, m0);
+        tma_load_2d(sB + s * B_TILE, &tma_b, &full[s], kb * BK, n0);
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== MMA issuer =====
+    constexpr uint32_t idesc = make_idesc(1, BM, BN);
+    int it = 0, t_local = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++t_local) {
+      const int a = t_local & 1;
+      const uint32_t aph = (t_local >> 1) & 1;
+      if (!mbar_wait(&acc_empty[a], aph ^ 1)) { atomicExch(&g_gemm_error, 4); return; }   // epilogue drained this accumulator
+      tc_fence_after_sync();
+      const uint32_t d_tmem = tmem_base + a * BN;
+      for (int kb = 0; kb < nk; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        if (!mbar_wait(&full[s], ph)) { atomicExch(&g_gemm_error, 2); return; }
+        tc_fence_after_sync();
+        const uint32_t a0 = smem_u32(sA + s * TILE_BYTES), b0 = smem_u32(sB + s * B_TILE);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          const uint64_t da = make_smem_desc(a0 + k * 32, 16, 1024, 2);
+          const uint64_t db = make_smem_desc(b0 + k * 32, 16, 1024, 2);
+          mma_bf16(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        mma_commit(&empty[s]);
+      }
+      mma_commit(&acc_full[a]);
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue =====
+    const int q = warp & 3;
+    constexpr int CHUNK = C_BF16 ? 64 : 32;           // columns per 128-byte chunk
+    uint8_t* slab0 = stage_base + q * 2 * SLAB;
+    int t_local = 0, chunk_it = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++t_local) {
+      const int m0 = (tile % tiles_m) * BM, n0 = (tile / tiles_m) * BN;
+      const int a = t_local & 1;
+      const uint32_t aph = (t_local >> 1) & 1;
+      const bool ok = mbar_wait(&acc_full[a], aph);
+      if (!ok && lane == 0) atomicExch(&g_gemm_error, 3);
+      tc_fence_after_sync();
+      const uint32_t t_addr = tmem_base + a * BN + (uint32_t(q * 32) << 16);
+      const bool row_live = m0 + q * 32 < M;          // whole slab out of range: nothing to store
+#pragma unroll 1
+      for (int c = 0; c < BN / CHUNK; ++c, ++chunk_it) {
+        if (n0 + c * CHUNK >= N) break;
+        uint8_t* slab = slab0 + (chunk_it & 1) * SLAB;
+        // the store that last used this slab (two chunks ago) must have read it
+        if (lane == 0) bulk_wait_read<1>();
+        __syncwarp();
+        uint32_t r[C_BF16 ? 64 : 32];
+        {
+          uint32_t (&r0)[16] = *reinterpret_cast<uint32_t (*)[16]>(&r[0]);
+          uint32_t (&r1)[16] = *reinterpret_cast<uint32_t (*)[16]>(&r[16]);
+          tmem_ld16_nowait(t_addr + c * CHUNK, r0);
+          tmem_ld16_nowait(t_addr + c * CHUNK + 16, r1);
+          if constexpr (C_BF16) {
+            uint32_t (&r2)[16] = *reinterpret_cast<uint32_t (*)[16]>(&r[32]);
+            uint32_t (&r3)[16] = *reinterpret_cast<uint32_t (*)[16]>(&r[48]);
+            tmem_ld16_nowait(t_addr + c * CHUNK + 32, r2);
+            tmem_ld16_nowait(t_addr + c * CHUNK + 48, r3);
+          }
+          tmem_ld_wait();
+        }
+        const int colbase = n0 + c * CHUNK;
+        // lane = output row; 16-byte pieces go to the 128B-swizzled position the C tensor map expects
+        const uint32_t row_off = smem_u32(slab) + lane * 128;
+        if constexpr (!C_BF16) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 v;
+            v.x = __uint_as_float(r[4 * j + 0]); v.y = __uint_as_float(r[4 * j + 1]);
+            v.z = __uint_as_float(r[4 * j + 2]); v.w = __uint_as_float(r[4 * j + 3]);
+            if (bias != nullptr) {
+              const int col = colbase + 4 * j;
+              if (col + 3 < N) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + col));
+                v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+              } else {
+                if (col + 0 < N) v.x += __ldg(bias + col + 0);
+                if (col + 1 < N) v.y += __ldg(bias + col + 1);
+                if (col + 2 < N) v.z += __ldg(bias + col + 2);
+              }
+            }
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row_off + ((j ^ (lane & 7)) << 4)),
+                         "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int col = colbase + 8 * j + 2 * e;
+              float lo = __uint_as_float(r[8 * j + 2 * e]), hi = __uint_as_float(r[8 * j + 2 * e + 1]);
+              if (bias != nullptr) {
+                if (col < N) lo += __ldg(bias + col);
+                if (col + 1 < N) hi += __ldg(bias + col + 1);
+              }
+              const __nv_bfloat162 h2 = __floats2bfloat162_rn(lo, hi);
+              pk[e] = *reinterpret_cast<const uint32_t*>(&h2);
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_off + ((j ^ (lane & 7)) << 4)),
+                         "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          if (ok && row_live) tma_store_2d(&tma_c, slab, colbase, m0 + q * 32, accumulate != 0);
+          bulk_commit();
+        }
+      }
+      // this warp's quarter of the accumulator is in registers / shared memory: hand it back to the MMA warp
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[a]);
+      if (retire != nullptr) {   // tile-retire count (see the non-persistent kernel): once per (tile, warp)
+        if (lane == 0) {
+          bulk_wait_all();
+          asm volatile("fence.proxy.async;" ::: "memory");
+          __threadfence();
+          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(retire) : "memory");
+        }
+        __syncwarp();
+      }
+    }
+    if (lane == 0) bulk_wait_all();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<512>(tmem_base);
+}
+
 // fp32 -> bf16 cast, optionally transposing [R, C] -> [C, R] (operands of the dW GEMMs)
 __global__ void cast_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -206,6 +424,27 @@ int make_map(CUtensorMap* map, const void* ptr, int rows, int k, int ld, int box
   return B200RNN_OK;
 }
 
+// C tile map for the persistent kernel's TMA stores: box = 128 bytes of columns x 32 rows, 128B swizzle.
+int make_c_map(CUtensorMap* map, void* ptr, int rows, int cols, int ldc, bool bf16_out) {
+  EncodeTiled enc = get_encode();
+  B200_REQUIRE(enc != nullptr, B200RNN_ECUDA, "gemm: cuTensorMapEncodeTiled entry point not available");
+  const int es = bf16_out ? 2 : 4;
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)ldc * es};
+  const cuuint32_t box[2] = {(cuuint32_t)(128 / es), 32u};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(map, bf16_out ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ptr, dims,
+                         strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  B200_REQUIRE(r == CUDA_SUCCESS, B200RNN_ECUDA, "gemm: cuTensorMapEncodeTiled(C) failed with %d", (int)r);
+  return B200RNN_OK;
+}
+
+bool persist_enabled() {   // B200RNN_GEMM_PERSIST=0 keeps every GEMM on the one-tile-per-CTA kernel
+  static const bool on = [] { const char* e = std::getenv("B200RNN_GEMM_PERSIST"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 }  // namespace
 }  // namespace b200rnn
 
@@ -230,6 +469,30 @@ extern "C" int b200rnn_gemm_bf16_retire(const void* A, const void* B, void* C, c
   const bool wide = !skinny && N >= 256 && ctas256 >= num_sms() / 2;
   const int bn = skinny ? 32 : (wide ? 256 : 128);
   CUtensorMap ma, mb;
+  // bulk shapes with a TMA-storable C (16-byte aligned rows): the persistent kernel
+  const int es = c_is_bf16 ? 2 : 4;
+  if (wide && persist_enabled() && (reinterpret_cast<uintptr_t>(C) & 15) == 0 && ((int64_t)ldc * es) % 16 == 0) {
+    CUtensorMap mc;
+    int rc2 = make_map(&ma, A, M, K, lda, BM, "A");
+    if (rc2) return rc2;
+    rc2 = make_map(&mb, B, N, K, ldb, persist::BN, "B");
+    if (rc2) return rc2;
+    rc2 = make_c_map(&mc, C, M, N, ldc, c_is_bf16 != 0);
+    if (rc2) return rc2;
+    static bool pattr = false;
+    if (!pattr) {
+      B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_persist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, persist::SMEM));
+      B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_persist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, persist::SMEM));
+      pattr = true;
+    }
+    const int tiles = ((M + BM - 1) / BM) * ((N + persist::BN - 1) / persist::BN);
+    const int grid_p = tiles < num_sms() ? tiles : num_sms();
+    if (retire_count) *retire_count = 4 * tiles;   // every epilogue warp counts each of its tile quarters
+    if (c_is_bf16) gemm_bf16_persist_kernel<true><<<grid_p, 256, persist::SMEM, (cudaStream_t)stream>>>(ma, mb, mc, bias, M, N, K, accumulate, retire_counter);
+    else gemm_bf16_persist_kernel<false><<<grid_p, 256, persist::SMEM, (cudaStream_t)stream>>>(ma, mb, mc, bias, M, N, K, accumulate, retire_counter);
+    B200_CHECK_LAUNCH();
+    return B200RNN_OK;
+  }
   int rc = make_map(&ma, A, M, K, lda, BM, "A");
   if (rc) return rc;
   rc = make_map(&mb, B, N, K, ldb, bn, "B");

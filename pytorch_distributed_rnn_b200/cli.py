@@ -70,22 +70,25 @@ def build_parser() -> argparse.ArgumentParser:
 
 
 def _ensure_synthetic_dataset(args) -> None:
-    """``--synthetic``: rank 0 writes the dataset if it is missing, the other ranks wait for the last file."""
+    """``--synthetic``: rank 0 writes the dataset if it is missing (atomically, marker file last); the other ranks
+    wait for the marker and fail loudly when it does not appear."""
+    import time
     from .data import synthetic
-    from .data.dataset import MotionDataset
+    from .data.dataset import _TensorCache
     from .parallel.process_group import env_rank_info
-    first, _ = MotionDataset.get_data_path(args.dataset_path, "train")
-    if first.exists():
+    if synthetic.is_complete(args.dataset_path):
         return
+    if _TensorCache(args.dataset_path).complete() and not any(Path(args.dataset_path).glob(".*.pt.tmp*")):
+        return   # a dataset written by someone else (e.g. the real preprocessed UCI-HAR cache): use it as it is
     rank, world, _ = env_rank_info()
     if rank == 0:
         synthetic.write_dataset(args.dataset_path, seed=args.seed or 0)
-    elif world > 1:
-        import time
-        last, _ = MotionDataset.get_data_path(args.dataset_path, "test")
-        deadline = time.monotonic() + 60.0
-        while not last.exists() and time.monotonic() < deadline:
-            time.sleep(0.1)
+        return
+    deadline = time.monotonic() + 120.0
+    while not synthetic.is_complete(args.dataset_path):
+        if time.monotonic() > deadline:
+            raise RuntimeError(f"--synthetic: rank 0 did not finish writing {args.dataset_path} within 120 s")
+        time.sleep(0.1)
 
 
 def main(argv=None):

@@ -32,11 +32,24 @@ def make_datasets(seed: int = 0, train: int = TRAIN_SIZE, valid: int = VALID_SIZ
     return make_split(train, seed, **kw), make_split(valid, seed + 1, **kw), make_split(test, seed + 2, **kw)
 
 
+DONE_MARKER = ".synthetic_complete"
+
+
 def write_dataset(path, seed: int = 0, **kw) -> Path:
+    """Write the six tensors; every file appears atomically (temp name + rename) and a marker file is created
+    after the last one, so a concurrent reader never sees a half-written dataset."""
+    import os
     path = Path(path)
     path.mkdir(parents=True, exist_ok=True)
     (xtr, ytr), (xv, yv), (xte, yte) = make_datasets(seed, **kw)
     for name, t in (("X_train", xtr), ("y_train", ytr), ("X_validation", xv), ("y_validation", yv),
                     ("X_test", xte), ("y_test", yte)):
-        torch.save(t, path / f"{name}.pt")
+        tmp = path / f".{name}.pt.tmp{os.getpid()}"
+        torch.save(t, tmp)
+        os.replace(tmp, path / f"{name}.pt")
+    (path / DONE_MARKER).write_text("ok\n")
     return path
+
+
+def is_complete(path) -> bool:
+    return (Path(path) / DONE_MARKER).exists()

@@ -9,7 +9,8 @@ pytestmark = pytest.mark.gpu
 
 @pytest.mark.parametrize("M,N,K", [(128, 128, 64), (128, 128, 256), (256, 384, 512), (1000, 520, 264), (64, 4096, 1024),
                                    (5, 24, 8), (4096, 128, 32),
-                                   (4096, 1024, 128), (3000, 1000, 72)])   # large enough for the 128x256 tiles
+                                   (4096, 1024, 128), (3000, 1000, 72),    # large enough for the 128x256 tiles
+                                   (4096, 2560, 192), (2176, 4356, 200)])  # persistent kernel: several tiles per CTA, tails
 def test_gemm_matches_fp32_reference(M, N, K):
     torch.manual_seed(M + N + K)
     a = torch.randn(M, K, device="cuda").bfloat16()
