@@ -19,7 +19,7 @@ for impl in reference own; do
   python - <<PY
 import json
 try:
-    d = json.load(open("$OUT/bench_motion_$impl.json"))
+    d = json.loads([l for l in open("$OUT/bench_motion_$impl.json") if l.startswith("{")][-1])
     print("motion $impl N=$N:", round(d["ms_per_step"], 4), "ms/step; e2e", round(d["e2e"]["ms_per_step"], 4), "; epoch", d.get("epoch"))
 except Exception as e:
     print("motion $impl failed:", e)
@@ -29,17 +29,27 @@ B200RNN_COMM=nccl $T bench.py --gpus $N --steps 50 --warmup 10 > $OUT/bench_moti
 python -c "
 import json
 try:
-    d = json.load(open('$OUT/bench_motion_own_nccl.json')); print('motion own (NCCL comm) N=$N:', round(d['ms_per_step'], 4), 'ms/step')
+    d = json.loads([l for l in open('$OUT/bench_motion_own_nccl.json') if l.startswith('{')][-1]); print('motion own (NCCL comm) N=$N:', round(d['ms_per_step'], 4), 'ms/step')
 except Exception as e: print('nccl A/B failed', e)"
 for impl in reference own; do
   $T bench.py --gpus $N --config scaled --impl $impl --steps 8 --warmup 3 > $OUT/bench_scaled_$impl.json 2> $OUT/bench_scaled_$impl.err
   python - <<PY
 import json
 try:
-    d = json.load(open("$OUT/bench_scaled_$impl.json"))
+    d = json.loads([l for l in open("$OUT/bench_scaled_$impl.json") if l.startswith("{")][-1])
     print("scaled $impl N=$N:", round(d["ms_per_step"], 3), "ms/step; e2e", round(d["e2e"]["ms_per_step"], 3), d.get("overlap_timeline_us"))
 except Exception as e:
     print("scaled $impl failed:", e)
 PY
 done
+if [ "$3" = "grid" ]; then   # the reference's rank-scaling experiment (fabfile.py:48-66), runs packed side by side on the box
+  timeout 900 python bench/sweep.py --dataset-path /tmp/b200rnn_motion --results $OUT/results_ranks.json --ranks ${4:-1,2,4} --repeats ${5:-2} --pack $N > $OUT/sweep_ranks.log 2>&1
+  python bench/analysis.py $OUT/results_ranks.json --plot $OUT/results_ranks.png > $OUT/results_ranks.md 2>> $OUT/sweep_ranks.log
+  tail -n 40 $OUT/results_ranks.md
+fi
+if [ "$3" = "network" ]; then   # the reference's network experiment (fabfile.py:130-191): injected delay before every flag publication
+  timeout 900 python bench/sweep.py --dataset-path /tmp/b200rnn_motion --results $OUT/results_network.json --ranks $N --network --delays ${4:-0,1,2,5,10,25,50,100,200,300,400} > $OUT/sweep_network.log 2>&1
+  python bench/analysis.py $OUT/results_network.json --network --plot $OUT/results_network.png > $OUT/results_network.md 2>> $OUT/sweep_network.log
+  tail -n 30 $OUT/results_network.md
+fi
 tail -n 3 $OUT/*.err | grep -v "^$" | tail -n 30
