@@ -23,10 +23,11 @@ Rank 0 prints ONE JSON line.  Two measurements per run:
   3 launches of this repo's kernels; the batch is read from the device-resident dataset through
   the sampler's index slice by the kernels' own loaders.
 * ``e2e``     — wall clock through the public API a user calls
-  (``FusedTrainEngine.train_steps_host``): every step assembles its batch on the host from the
-  dataset and the sampler's indices (index_select into pinned memory — what the reference's
-  DataLoader does with __getitem__ + collate), copies it to the GPU and reads the step's loss back
-  to the host (assembly and copies pipelined with compute).
+  (``FusedTrainEngine.train_steps_dataset``): the dataset sits in pinned host memory; every step
+  the sampler's index slice goes to the GPU, the gather kernel pulls that step's rows out of the
+  pinned dataset over PCIe into a device batch (what the reference's DataLoader does with
+  __getitem__ + collate + a host->device copy), and the step's loss is read back to the host;
+  transfers run on a side stream under the previous step's compute.
 * ``epoch``   — the BASELINE.md metric itself: wall clock of ONE epoch (6 912 samples: 4 full
   batches + the partial one) through ``Trainer.train(1)`` (src/motion/trainer/base.py:93-96), cold
   (first call, includes buffer allocation) and warm (second call); max over ranks.
@@ -216,33 +217,22 @@ def run_own(args):
     # ---------------- end-to-end through the public API ----------------
     # Every step's batch is ASSEMBLED on the host inside the timed region (rows of the dataset selected by the
     # sampler's indices into pinned staging memory), then copied to the device; its loss is read back.
-    ring = 4   # pinned staging buffers: the pipeline keeps at most two copies in flight
-    y_flat = y_all.view(-1)
-    pin_x = [torch.empty(per_rank, SEQ_LEN, FEATURES).pin_memory() for _ in range(ring)]
-    pin_y = [torch.empty(per_rank, dtype=torch.int64).pin_memory() for _ in range(ring)]
-    idx_host = [step_indices(s) for s in range(max(W, 3) + K)]
-
-    def host_batches(first, count):
-        for s in range(first, first + count):
-            k = s % ring
-            torch.index_select(x_all, 0, idx_host[s], out=pin_x[k])
-            torch.index_select(y_flat, 0, idx_host[s], out=pin_y[k])
-            yield pin_x[k], pin_y[k]
-
-    for _ in engine.train_steps_host(host_batches(0, max(W, 3))):
+    x_pin, y_pin = x_all.pin_memory(), y_all.pin_memory()       # the dataset, pinned once (as a DataLoader would pin batches)
+    idx_host = [step_indices(s) for s in range(max(W, 3) + K)]  # the sampler's output: one index slice per step
+    for _ in engine.train_steps_dataset(x_pin, y_pin, idx_host[:max(W, 3)]):
         pass
     barrier_sync(world, dev)
     t_c = time.time()
     t0 = time.perf_counter()
     n_results = 0
-    for loss, correct in engine.train_steps_host(host_batches(max(W, 3), K)):
+    for loss, correct in engine.train_steps_dataset(x_pin, y_pin, idx_host[max(W, 3):]):
         n_results += 1
     assert n_results == K
     barrier_sync(world, dev)
     e2e_s = time.perf_counter() - t0
     t_d = time.time()
     e2e_s = max_over_ranks(e2e_s, world, dev)
-    h2d = world * (pin_x[0].numel() * 4 + pin_y[0].numel() * 8)
+    h2d = world * per_rank * (SEQ_LEN * FEATURES * 4 + 8 + 8)   # rows + labels + the index slice
     d2h = world * 8
 
     # ---------------- one epoch through the trainer (the BASELINE.md metric) ----------------
@@ -272,10 +262,10 @@ def run_own(args):
                        "baseline_number": "1922.7 samples/s = 6912/3.595 s, reference local bs1440 on its fast host"},
             "e2e": {"value": GLOBAL_BATCH * K / e2e_s, "unit": "samples/s", "ms_per_step": 1e3 * e2e_s / K,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "api": "FusedTrainEngine.train_steps_host(host_batches) -> yields (loss, correct) per step",
-                    "inputs": "every step, inside the timed region: host-side batch assembly (index_select of the dataset "
-                              "rows picked by the sampler into pinned memory), H2D copy of that batch (side stream, "
-                              "overlapping the previous step) and D2H read of its loss (one-step lag)"},
+                    "api": "FusedTrainEngine.train_steps_dataset(pinned_features, pinned_labels, index_slices) -> yields (loss, correct) per step",
+                    "inputs": "every step, inside the timed region: the sampler's index slice goes host -> device, the gather kernel "
+                              "pulls that batch's rows from the PINNED HOST dataset into device memory (side stream, overlapping the "
+                              "previous step), and the step's loss is read device -> host (one-step lag); nothing is pre-collated"},
             "epoch": epoch,
             "gpu_launches": launches,
             "launches_per_step": launches / K,
@@ -345,25 +335,14 @@ def run_own_scaled(args):
     dev_ms = max_over_ranks(sum(a.elapsed_time(b) for a, b in ev), world, dev)
     last = engine.metrics[(engine.n_steps - 1) % engine.METRIC_RING].cpu()
 
-    ring = 4
-    y_flat = y_all.view(-1)
-    pin_x = [torch.empty(per_rank, T, FEATURES).pin_memory() for _ in range(ring)]
-    pin_y = [torch.empty(per_rank, dtype=torch.int64).pin_memory() for _ in range(ring)]
+    x_pin, y_pin = x_all.pin_memory(), y_all.pin_memory()
     idx_host = [step_indices(s) for s in range(max(W, 3) + K)]
-
-    def host_batches(first, count):
-        for s in range(first, first + count):
-            k = s % ring
-            torch.index_select(x_all, 0, idx_host[s], out=pin_x[k])
-            torch.index_select(y_flat, 0, idx_host[s], out=pin_y[k])
-            yield pin_x[k], pin_y[k]
-
-    for _ in engine.train_steps_host(host_batches(0, max(W, 3))):
+    for _ in engine.train_steps_dataset(x_pin, y_pin, idx_host[:max(W, 3)]):
         pass
     barrier_sync(world, dev)
     t_c = time.time()
     t0 = time.perf_counter()
-    n_results = sum(1 for _ in engine.train_steps_host(host_batches(max(W, 3), K)))
+    n_results = sum(1 for _ in engine.train_steps_dataset(x_pin, y_pin, idx_host[max(W, 3):]))
     assert n_results == K
     barrier_sync(world, dev)
     e2e_s = max_over_ranks(time.perf_counter() - t0, world, dev)
@@ -395,9 +374,10 @@ def run_own_scaled(args):
                        "l2": "256 MiB L2 flush between timed steps, outside the CUDA-event brackets",
                        "timing": "per-step CUDA events on the launching stream, summed, max over ranks"},
             "e2e": {"value": gb * K / e2e_s, "unit": "samples/s", "ms_per_step": 1e3 * e2e_s / K,
-                    "h2d_bytes_per_step": world * (pin_x[0].numel() * 4 + pin_y[0].numel() * 8), "d2h_bytes_per_step": world * 8,
-                    "api": "LayeredTrainEngine.train_steps_host(host_batches) -> yields (loss, correct) per step",
-                    "inputs": "every step, inside the timed region: host-side batch assembly into pinned memory, H2D copy, D2H loss read"},
+                    "h2d_bytes_per_step": world * per_rank * (T * FEATURES * 4 + 8 + 8), "d2h_bytes_per_step": world * 8,
+                    "api": "LayeredTrainEngine.train_steps_dataset(pinned_features, pinned_labels, index_slices) -> yields (loss, correct) per step",
+                    "inputs": "every step, inside the timed region: index slice host -> device, gather of the batch's rows from the pinned "
+                              "host dataset by the GPU, D2H loss read"},
             "gpu_launches": launches, "launches_per_step": launches / K, "clocks": clocks,
             "overlap_timeline_us": timeline,
             "final_loss": float(last[0]) / per_rank,

@@ -39,6 +39,16 @@ class HostStepsMixin:
     """End-to-end stepping from HOST batches for an engine that provides ``train_step(x_dev, y_dev)``, ``device``,
     ``_copy_stream`` and ``_host_metrics`` (shared by the small-hidden and the layered large-hidden engines)."""
 
+    def train_steps_dataset(self, feats_pinned: torch.Tensor, labels_pinned: torch.Tensor, index_batches):
+        """End-to-end training from a dataset that lives in PINNED HOST memory, given the sampler's index slices
+        (an iterable of int64 host tensors, one per step) — the DataLoader + DistributedSampler of the reference
+        (src/motion/trainer/base.py:56-60,107) without a host-side collate: per step the index slice goes to the
+        device (a few KB) and the K11 gather kernel pulls that step's rows straight out of the pinned dataset over
+        PCIe into a device batch, on a side stream while the previous step computes; the step's loss is read back
+        with a one-step lag.  Every step still moves its whole input host -> device and its result device -> host.
+        Generator: yields ``(mean loss, correct count)`` per step, in order."""
+        return _train_steps_dataset(self, feats_pinned, labels_pinned, index_batches)
+
     def train_step_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> Tuple[float, int]:
         """End-to-end step from host memory: H2D copy of the batch (pass pinned tensors for an async
         DMA), the 3-launch training step, and a D2H read of this step's result.
@@ -115,6 +125,71 @@ class HostStepsMixin:
         j, Bj = pending
         res_ready[j].synchronize()
         yield float(results[j][0]) / Bj, int(round(float(results[j][1])))
+
+
+def _train_steps_dataset(self, feats_pinned: torch.Tensor, labels_pinned: torch.Tensor, index_batches):
+    """See HostStepsMixin.train_steps_dataset."""
+    dev, lib = self.device, _native.lib()
+    if not (feats_pinned.is_pinned() and labels_pinned.is_pinned()):
+        raise ValueError("train_steps_dataset: the dataset tensors must live in pinned host memory (tensor.pin_memory())")
+    if feats_pinned.dtype != torch.float32 or labels_pinned.dtype != torch.int64:
+        raise ValueError("train_steps_dataset: features fp32, labels int64")
+    T, I = feats_pinned.shape[1], feats_pinned.shape[2]
+    labels_flat = labels_pinned.view(-1)
+    main = torch.cuda.current_stream(dev)
+    if self._copy_stream is None:
+        self._copy_stream = torch.cuda.Stream(dev)
+    cs = self._copy_stream
+    slots, idx_pin, idx_dev = [None, None], [None, None], [None, None]
+    copied = [torch.cuda.Event(), torch.cuda.Event()]
+    consumed = [torch.cuda.Event(), torch.cuda.Event()]
+    results = [torch.zeros(2, dtype=torch.float32).pin_memory() for _ in range(2)]
+    res_ready = [torch.cuda.Event(), torch.cuda.Event()]
+
+    def stage(i, idx):
+        B = idx.numel()
+        if slots[i] is None or slots[i][0].shape[0] != B:
+            slots[i] = (torch.empty(B, T, I, dtype=torch.float32, device=dev), torch.empty(B, dtype=torch.int64, device=dev))
+            idx_pin[i] = torch.empty(B, dtype=torch.int64).pin_memory()
+            idx_dev[i] = torch.empty(B, dtype=torch.int64, device=dev)
+        with torch.cuda.stream(cs):
+            cs.wait_event(consumed[i])            # the step that last used this slot (and its index buffer) has finished
+            idx_pin[i].copy_(idx)
+            idx_dev[i].copy_(idx_pin[i], non_blocking=True)
+            # the GPU pulls the batch's rows out of the pinned dataset itself (peer reads over PCIe)
+            _native.check(lib.b200rnn_gather_batch(feats_pinned.data_ptr(), labels_flat.data_ptr(), idx_dev[i].data_ptr(), B,
+                                                   T * I, slots[i][0].data_ptr(), slots[i][1].data_ptr(), cs.cuda_stream),
+                          "gather_batch")
+            copied[i].record(cs)
+
+    it = iter(index_batches)
+    nxt = next(it, None)
+    if nxt is None:
+        return
+    for e in consumed:
+        e.record(main)
+    stage(0, nxt)
+    s, pending = 0, None
+    while nxt is not None:
+        i = s & 1
+        cur_B = nxt.numel()
+        nxt = next(it, None)
+        if nxt is not None:
+            stage(i ^ 1, nxt)
+        main.wait_event(copied[i])
+        m = self.train_step(slots[i][0], slots[i][1])
+        consumed[i].record(main)
+        results[i].copy_(m, non_blocking=True)
+        res_ready[i].record(main)
+        if pending is not None:
+            j, Bj = pending
+            res_ready[j].synchronize()
+            yield float(results[j][0]) / Bj, int(round(float(results[j][1])))
+        pending = (i, cur_B)
+        s += 1
+    j, Bj = pending
+    res_ready[j].synchronize()
+    yield float(results[j][0]) / Bj, int(round(float(results[j][1])))
 
 
 class FusedTrainEngine(HostStepsMixin):

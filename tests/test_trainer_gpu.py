@@ -62,3 +62,25 @@ def test_pipelined_host_steps_match_serial_steps():
     piped = list(b.train_steps_host(zip(xs, ys)))
     assert serial == piped
     assert torch.equal(a.arena.flat, b.arena.flat)
+
+
+def test_pinned_dataset_steps_match_device_resident_steps():
+    """train_steps_dataset (index slice -> device, rows pulled from the pinned host dataset by the gather kernel)
+    must train exactly like stepping through the same index slices of a device-resident copy."""
+    from pytorch_distributed_rnn_b200.ops.engine import FusedTrainEngine
+    torch.manual_seed(5)
+    N, B = 500, 96
+    feats, labels = torch.randn(N, 32, 9), torch.randint(0, 6, (N, 1))
+    idx = [torch.randperm(N)[:B] for _ in range(5)] + [torch.randperm(N)[:40]]      # last batch partial
+    torch.manual_seed(3)
+    a = FusedTrainEngine(MotionModel(9, 32, 2, 6).cuda())
+    torch.manual_seed(3)
+    b = FusedTrainEngine(MotionModel(9, 32, 2, 6).cuda())
+    fd, ld = feats.cuda(), labels.cuda()
+    want = []
+    for i in idx:
+        m = a.train_step_gather(fd, ld, i.cuda()).cpu()
+        want.append((float(m[0]) / i.numel(), int(round(float(m[1])))))
+    got = list(b.train_steps_dataset(feats.pin_memory(), labels.pin_memory(), idx))
+    assert got == want
+    assert torch.equal(a.arena.flat, b.arena.flat)
