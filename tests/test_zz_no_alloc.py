@@ -80,3 +80,39 @@ def test_static_scratch_backward_refuses_oversized_shape():
     assert rc == -4  # B200RNN_ETOOBIG
     msg = lib.b200rnn_last_error().decode()
     assert "scratch" in msg and "b200rnn_lstm_bwd" in msg
+
+
+def test_static_scratch_backward_with_output_gradients_three_layers():
+    """Same comparison on the other gradient sources: an explicit gradient of the whole output sequence plus final-state
+    gradients instead of the fused head, three layers, a batch small enough for the layer wavefront (the built-in
+    scratch then also carries the inter-layer dx hand-off, sentinels included)."""
+    lib = _native.lib()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    B, T, I, L = 24, 33, 9, 3
+    d, params, x, _, stash, sp = _case(lib, 21, B, T, I, L, 6, dev)
+    g = torch.Generator().manual_seed(99)
+    d_out = torch.randn(B, T, 32, generator=g).to(dev)
+    d_hn = torch.randn(L, B, 32, generator=g).to(dev)
+    d_cn = torch.randn(L, B, 32, generator=g).to(dev)
+    assert lib.b200rnn_rnn_small_bwd_wave(C.byref(d)) == 1          # the shape does run as a wavefront
+    scratch = torch.empty(lib.b200rnn_rnn_bwd_scratch_floats(C.byref(d)), dtype=torch.float32, device=dev)
+    rb, nc = C.c_int32(), C.c_int32()
+    _native.check(lib.b200rnn_rnn_small_tiling(C.byref(d), C.byref(rb), C.byref(nc)))
+    outs = []
+    for rep in range(2):     # twice: what the first call leaves in the shared array must not leak into the second
+        _native.check(lib.b200rnn_lstm_bwd(C.byref(d), params.data_ptr(), x.data_ptr(), stash.data_ptr(), None, 1.0,
+                                           d_out.data_ptr(), d_hn.data_ptr(), d_cn.data_ptr(), scratch.data_ptr(), sp), "bwd")
+        want = torch.empty(d.n_params + 2, dtype=torch.float32, device=dev)
+        _native.check(lib.b200rnn_reduce_rows(scratch.data_ptr(), nc.value, d.n_params + 2, want.data_ptr(), 0, sp), "reduce")
+        got = torch.full((d.n_params + 2,), float("nan"), dtype=torch.float32, device=dev)
+        _native.check(lib.b200rnn_lstm_bwd_static(C.byref(d), params.data_ptr(), x.data_ptr(), stash.data_ptr(), None, 1.0,
+                                                  d_out.data_ptr(), d_hn.data_ptr(), d_cn.data_ptr(), got.data_ptr(), sp),
+                      "bwd_static")
+        torch.cuda.synchronize()
+        scale = float(want[:-2].abs().max())
+        assert bool(torch.isfinite(got).all())
+        assert torch.allclose(got, want, atol=2e-5 * max(scale, 1.0), rtol=1e-4), float((got - want).abs().max())
+        d_out = d_out * 0.5 + 1.0
+        outs.append(got)
+    assert not torch.equal(outs[0], outs[1])
+    _native.assert_device_healthy()
