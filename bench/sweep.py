@@ -156,11 +156,41 @@ def main():
             run_training(train_runs(ranks, a.repeats), a.dataset_path, a.results)
         return
     n = max(ranks)
-    for d in [int(x) for x in a.delays.split(",")]:
-        runs = [{"trainer": tr, "hosts": n, "slots": 1,
-                 "parameters": {"--batch-size": 1440, "--epochs": 1, "--seed": 123456789, "--no-validation": ""}}
-                for tr in ("distributed", "horovod")]
-        run_training(runs, a.dataset_path, a.results, env={"B200RNN_DELAY_NS": str(d * 1000)}, tag=f"delay={d}")
+    run_network(a, n)
+
+
+def run_network(a, n):
+    """O2: the delay experiment.  One job per trainer sweeps all delays in-process (`--delay-sweep-us`: start-up costs
+    seconds, an epoch milliseconds); its log is split at the delay markers into one result entry per (trainer, delay),
+    in the reference's network-results schema."""
+    import re
+    for tr in ("distributed", "horovod"):
+        run = {"trainer": tr, "hosts": n, "slots": 1, "repeat": 0,
+               "parameters": {"--batch-size": 1440, "--epochs": 1, "--seed": 123456789, "--no-validation": "",
+                              "--delay-sweep-us": a.delays}}
+        cmd = get_command(run, a.dataset_path)
+        command = " ".join(cmd)
+        results = load_results(a.results)
+        if any(r.get("sweep_command") == command for r in results):
+            print(f"skip (already recorded): {command}")
+            continue
+        print(command, flush=True)
+        cp = subprocess.run(cmd, capture_output=True, text=True, env=dict(os.environ, PYTHONPATH=str(ROOT)), cwd=str(ROOT))
+        parts = re.split(r"^.*Injected delay: (\d+) us.*$", cp.stderr, flags=re.M)
+        # parts = [preamble, d0, log0, d1, log1, ...] with every rank's log contributing one segment per delay
+        by_delay = {}
+        for d, log in zip(parts[1::2], parts[2::2]):
+            by_delay[d] = by_delay.get(d, "") + log
+        for d, log in by_delay.items():
+            entry = {"command": f"{command}  #delay={d}", "sweep_command": command, "trainer": tr, "stdout": "", "stderr": log,
+                     "returncode": cp.returncode, "config": {k: run[k] for k in ("trainer", "hosts", "slots", "parameters")}}
+            entry.update(tag_fields(f"delay={d}"))
+            results.append(entry)
+        if len(parts) < 3:   # the job failed before the first marker: record it as the reference records failed runs
+            results.append({"command": command, "sweep_command": command, "trainer": tr, "stdout": cp.stdout, "stderr": cp.stderr,
+                            "returncode": cp.returncode, "config": {k: run[k] for k in ("trainer", "hosts", "slots", "parameters")}})
+        with open(a.results, "w") as f:
+            json.dump({"results": results}, f)
 
 
 if __name__ == "__main__":

@@ -49,6 +49,10 @@ EXTENSION_FLAGS = (
     ("history-path", dict(default=None, type=Path)),
     ("synthetic", dict(action="store_true",
                        help="write a synthetic dataset of the reference's shape to --dataset-path if none is there")),
+    ("delay-sweep-us", dict(default=None, type=str,
+                            help="network experiment in one process: comma list of delays (us) injected before every flag "
+                                 "publication of the in-kernel collectives; the run is repeated once per value after an "
+                                 "untimed warm-up, each with its own performance line (fabfile.py:130-191 ran one job per rule)")),
 )
 
 
