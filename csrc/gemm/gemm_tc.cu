@@ -374,6 +374,257 @@ gemm_bf16_persist_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   if (warp == 2) tmem_dealloc<512>(tmem_base);
 }
 
+// ---------------------------------------------------------------------------
+// CTA-pair form of the persistent kernel (tcgen05 `cta_group::2`): two CTAs of a cluster — two SMs of one TPC —
+// compute one 256 x 256 output tile.  Each CTA stages ITS 128 rows of A and ITS 128 columns of B (32 KiB per stage
+// instead of 48, so the ring is 6 deep), the leader CTA's single MMA thread issues M = 256 instructions that drive
+// both SMs' tensor cores (twice the tensor work per issued instruction: a lone issuer no longer caps the pipe), and
+// every CTA drains its own 128 x 256 half of the accumulator from its own TMEM.  Cross-CTA signalling:
+//   * both producers' TMA loads complete on the LEADER's `full[s]` (cp.async.bulk.tensor ... cta_group::2 with the
+//     leader's barrier address): the MMA thread waits once for all four boxes of a stage;
+//   * tcgen05.commit ... multicast::cluster arrives on `empty[s]` / `acc_full[a]` of BOTH CTAs;
+//   * the peer's epilogue warps arrive remotely on the leader's `acc_empty[a]`.
+// All operands and the tensor maps cover this GPU's memory only.
+// ---------------------------------------------------------------------------
+namespace pair {
+constexpr int BN = 256, NACC = 2, STG = 6;
+constexpr int A_TILE = BM * BK * 2;                               // 16 KiB: my 128 rows of A
+constexpr int B_TILE = (BN / 2) * BK * 2;                         // 16 KiB: my 128 columns of B
+constexpr int RING = STG * (A_TILE + B_TILE);                     // 192 KiB
+constexpr int SMEM = RING + persist::STAGING + 256 + 1024;
+}  // namespace pair
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `local` (an address in my own shared memory) inside CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* map, uint32_t bar_cluster_addr, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(bar_cluster_addr), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void mma_bf16_pair(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void mma_commit_pair(uint64_t* bar) {   // arrives on `bar` of both CTAs of the pair
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
+}
+// bounded wait that also gives up as soon as any role has reported a pipeline error
+__device__ __forceinline__ bool mbar_wait_abortable(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return true;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 2000000000LL || *reinterpret_cast<volatile int*>(&g_gemm_error) != 0) return false;
+  }
+  return true;
+}
+
+template <bool C_BF16>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(256, 1)
+gemm_bf16_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                      const __grid_constant__ CUtensorMap tma_c, const float* __restrict__ bias, int M, int N, int K,
+                      int accumulate, unsigned int* __restrict__ retire) {
+  using namespace pair;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + STG * A_TILE;
+  uint8_t* stage_base = smem + RING;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + RING + persist::STAGING);
+  uint64_t* empty = full + STG;
+  uint64_t* acc_full = empty + STG;
+  uint64_t* acc_empty = acc_full + NACC;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + NACC);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();          // 0 = leader (issues the MMAs)
+  const int pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+  const int nk = (K + BK - 1) / BK;
+  const int tiles_m = (M + 2 * BM - 1) / (2 * BM), tiles_n = (N + BN - 1) / BN;
+  const int n_tiles = tiles_m * tiles_n;
+
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&tma_a); tma_prefetch_desc(&tma_b); tma_prefetch_desc(&tma_c); }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < STG; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < NACC; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_empty[i], 8); }   // 4 warps x 2 CTAs
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  __syncwarp();
+  cluster_sync_all();     // both CTAs' barriers exist before anybody signals across the pair
+  tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer (both CTAs): my half of each operand, completion on the LEADER's full[s] =====
+    int it = 0;
+    for (int tile = pair_id; tile < n_tiles; tile += n_pairs) {
+      const int m0 = (tile % tiles_m) * 2 * BM + (int)rank * BM, n0 = (tile / tiles_m) * BN + (int)rank * (BN / 2);
+      for (int kb = 0; kb < nk; ++kb, ++it) {
+        const int s = it % STG;
+        const uint32_t ph = (it / STG) & 1;
+        if (!mbar_wait_abortable(&empty[s], ph ^ 1)) { atomicExch(&g_gemm_error, 1); break; }
+        const uint32_t lead_full = mapa_u32(smem_u32(&full[s]), 0);
+        if (rank == 0) mbar_expect_tx(&full[s], 2 * (A_TILE + B_TILE));   // four boxes land per stage
+        tma_load_2d_pair(sA + s * A_TILE, &tma_a, lead_full, kb * BK, m0);
+        tma_load_2d_pair(sB + s * B_TILE, &tma_b, lead_full, kb * BK, n0);
+      }
+    }
+  } else if (warp == 1 && lane == 0 && rank == 0) {
+    // ===== MMA issuer (leader CTA only) =====
+    constexpr uint32_t idesc = make_idesc(1, 2 * BM, BN);
+    int it = 0, t_local = 0;
+    bool ok = true;
+    for (int tile = pair_id; tile < n_tiles && ok; tile += n_pairs, ++t_local) {
+      const int a = t_local & 1;
+      const uint32_t aph = (t_local >> 1) & 1;
+      if (!mbar_wait_abortable(&acc_empty[a], aph ^ 1)) { atomicExch(&g_gemm_error, 4); break; }
+      tc_fence_after_sync();
+      const uint32_t d_tmem = tmem_base + a * BN;
+      for (int kb = 0; kb < nk; ++kb, ++it) {
+        const int s = it % STG;
+        const uint32_t ph = (it / STG) & 1;
+        if (!mbar_wait_abortable(&full[s], ph)) { atomicExch(&g_gemm_error, 2); ok = false; break; }
+        tc_fence_after_sync();
+        const uint32_t a0 = smem_u32(sA + s * A_TILE), b0 = smem_u32(sB + s * B_TILE);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k) {
+          const uint64_t da = make_smem_desc(a0 + k * 32, 16, 1024, 2);
+          const uint64_t db = make_smem_desc(b0 + k * 32, 16, 1024, 2);
+          mma_bf16_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        mma_commit_pair(&empty[s]);
+      }
+      if (ok) mma_commit_pair(&acc_full[a]);
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue (both CTAs): my 128 rows of the tile =====
+    const int q = warp & 3;
+    constexpr int CHUNK = C_BF16 ? 64 : 32;
+    uint8_t* slab0 = stage_base + q * 2 * persist::SLAB;
+    int t_local = 0, chunk_it = 0;
+    for (int tile = pair_id; tile < n_tiles; tile += n_pairs, ++t_local) {
+      const int m0 = (tile % tiles_m) * 2 * BM + (int)rank * BM, n0 = (tile / tiles_m) * BN;
+      const int a = t_local & 1;
+      const uint32_t aph = (t_local >> 1) & 1;
+      const bool ok = mbar_wait_abortable(&acc_full[a], aph);
+      if (!ok && lane == 0) atomicExch(&g_gemm_error, 3);
+      tc_fence_after_sync();
+      const uint32_t t_addr = tmem_base + a * BN + (uint32_t(q * 32) << 16);
+      const bool row_live = m0 + q * 32 < M;
+#pragma unroll 1
+      for (int c = 0; c < BN / CHUNK; ++c, ++chunk_it) {
+        if (n0 + c * CHUNK >= N) break;
+        uint8_t* slab = slab0 + (chunk_it & 1) * persist::SLAB;
+        if (lane == 0) bulk_wait_read<1>();
+        __syncwarp();
+        uint32_t r[C_BF16 ? 64 : 32];
+        {
+          uint32_t (&r0)[16] = *reinterpret_cast<uint32_t (*)[16]>(&r[0]);
+          uint32_t (&r1)[16] = *reinterpret_cast<uint32_t (*)[16]>(&r[16]);
+          tmem_ld16_nowait(t_addr + c * CHUNK, r0);
+          tmem_ld16_nowait(t_addr + c * CHUNK + 16, r1);
+          if constexpr (C_BF16) {
+            uint32_t (&r2)[16] = *reinterpret_cast<uint32_t (*)[16]>(&r[32]);
+            uint32_t (&r3)[16] = *reinterpret_cast<uint32_t (*)[16]>(&r[48]);
+            tmem_ld16_nowait(t_addr + c * CHUNK + 32, r2);
+            tmem_ld16_nowait(t_addr + c * CHUNK + 48, r3);
+          }
+          tmem_ld_wait();
+        }
+        const int colbase = n0 + c * CHUNK;
+        const uint32_t row_off = smem_u32(slab) + lane * 128;
+        if constexpr (!C_BF16) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 v;
+            v.x = __uint_as_float(r[4 * j + 0]); v.y = __uint_as_float(r[4 * j + 1]);
+            v.z = __uint_as_float(r[4 * j + 2]); v.w = __uint_as_float(r[4 * j + 3]);
+            if (bias != nullptr) {
+              const int col = colbase + 4 * j;
+              if (col + 3 < N) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + col));
+                v.x += b4.x; v.y += b4.y; v.z += b4.z; v.w += b4.w;
+              } else {
+                if (col + 0 < N) v.x += __ldg(bias + col + 0);
+                if (col + 1 < N) v.y += __ldg(bias + col + 1);
+                if (col + 2 < N) v.z += __ldg(bias + col + 2);
+              }
+            }
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(row_off + ((j ^ (lane & 7)) << 4)),
+                         "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            uint32_t pk[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int col = colbase + 8 * j + 2 * e;
+              float lo = __uint_as_float(r[8 * j + 2 * e]), hi = __uint_as_float(r[8 * j + 2 * e + 1]);
+              if (bias != nullptr) {
+                if (col < N) lo += __ldg(bias + col);
+                if (col + 1 < N) hi += __ldg(bias + col + 1);
+              }
+              const __nv_bfloat162 h2 = __floats2bfloat162_rn(lo, hi);
+              pk[e] = *reinterpret_cast<const uint32_t*>(&h2);
+            }
+            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(row_off + ((j ^ (lane & 7)) << 4)),
+                         "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          if (ok && row_live) tma_store_2d(&tma_c, slab, colbase, m0 + q * 32, accumulate != 0);
+          bulk_commit();
+        }
+      }
+      // my quarter of my CTA's accumulator half is out of TMEM: tell the leader's MMA thread
+      tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(mapa_u32(smem_u32(&acc_empty[a]), 0));
+      if (retire != nullptr) {
+        if (lane == 0) {
+          bulk_wait_all();
+          asm volatile("fence.proxy.async;" ::: "memory");
+          __threadfence();
+          asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(retire) : "memory");
+        }
+        __syncwarp();
+      }
+    }
+    if (lane == 0) bulk_wait_all();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  __syncwarp();
+  cluster_sync_all();     // nobody leaves (or frees TMEM / shared memory) while the pair still works on a tile
+  if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(512) : "memory");
+}
+
 // fp32 -> bf16 cast, optionally transposing [R, C] -> [C, R] (operands of the dW GEMMs)
 __global__ void cast_bf16_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -440,6 +691,10 @@ int make_c_map(CUtensorMap* map, void* ptr, int rows, int cols, int ldc, bool bf
   return B200RNN_OK;
 }
 
+int pair_mode() {   // B200RNN_GEMM_PAIR=0 keeps the bulk GEMMs on the single-CTA persistent kernel
+  static const int v = [] { const char* e = std::getenv("B200RNN_GEMM_PAIR"); return (e && e[0] == '0') ? 0 : 1; }();
+  return v;
+}
 bool persist_enabled() {   // B200RNN_GEMM_PERSIST=0 keeps every GEMM on the one-tile-per-CTA kernel
   static const bool on = [] { const char* e = std::getenv("B200RNN_GEMM_PERSIST"); return !(e && e[0] == '0'); }();
   return on;
@@ -484,6 +739,24 @@ extern "C" int b200rnn_gemm_bf16_retire(const void* A, const void* B, void* C, c
       B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_persist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, persist::SMEM));
       B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_persist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, persist::SMEM));
       pattr = true;
+    }
+    if (pair_mode() && M >= 2 * BM) {
+      // CTA-pair kernel: B box = my 128 columns
+      rc2 = make_map(&mb, B, N, K, ldb, pair::BN / 2, "B");
+      if (rc2) return rc2;
+      static bool pair_attr = false;
+      if (!pair_attr) {
+        B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_pair_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::SMEM));
+        B200_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_pair_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, pair::SMEM));
+        pair_attr = true;
+      }
+      const int tiles2 = ((M + 2 * BM - 1) / (2 * BM)) * ((N + pair::BN - 1) / pair::BN);
+      const int pairs = tiles2 < num_sms() / 2 ? tiles2 : num_sms() / 2;
+      if (retire_count) *retire_count = 8 * tiles2;   // 4 epilogue warps x 2 CTAs per tile
+      if (c_is_bf16) gemm_bf16_pair_kernel<true><<<2 * pairs, 256, pair::SMEM, (cudaStream_t)stream>>>(ma, mb, mc, bias, M, N, K, accumulate, retire_counter);
+      else gemm_bf16_pair_kernel<false><<<2 * pairs, 256, pair::SMEM, (cudaStream_t)stream>>>(ma, mb, mc, bias, M, N, K, accumulate, retire_counter);
+      B200_CHECK_LAUNCH();
+      return B200RNN_OK;
     }
     const int tiles = ((M + BM - 1) / BM) * ((N + persist::BN - 1) / persist::BN);
     const int grid_p = tiles < num_sms() ? tiles : num_sms();
