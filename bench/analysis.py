@@ -69,12 +69,9 @@ def table(rows, network=False):
     return "\n".join(out)
 
 
-def plot(rows, path, network=False):
-    import matplotlib
-    matplotlib.use("Agg")
-    import matplotlib.pyplot as plt
-    fig, ax = plt.subplots(figsize=(6, 4))
+def _series(rows, network):
     xs = "rule_value" if network else "ranks"
+    out = {}
     for tr in sorted({r["trainer"] for r in rows}):
         pts = defaultdict(list)
         for r in rows:
@@ -82,12 +79,65 @@ def plot(rows, path, network=False):
                 pts[r[xs]].append(r["seconds"])
         if pts:
             k = sorted(pts)
-            ax.plot(k, [statistics.mean(pts[x]) for x in k], marker="o", label=tr)
-    ax.set_xlabel("injected delay (us)" if network else "ranks (GPUs)")
+            out[tr] = (k, [statistics.mean(pts[x]) for x in k])
+    return out
+
+
+def plot(rows, path, network=False):
+    """Training time vs ranks (or injected delay) per trainer.  matplotlib (Agg) when it is installed, else a
+    dependency-free SVG with the same content (``path`` then gets the .svg suffix); returns the file written."""
+    series = _series(rows, network)
+    xlabel = "injected delay (us)" if network else "ranks (GPUs)"
+    try:
+        import matplotlib
+        matplotlib.use("Agg")
+        import matplotlib.pyplot as plt
+    except ImportError:
+        return _plot_svg(series, Path(path).with_suffix(".svg"), xlabel)
+    fig, ax = plt.subplots(figsize=(6, 4))
+    for tr, (k, v) in series.items():
+        ax.plot(k, v, marker="o", label=tr)
+    ax.set_xlabel(xlabel)
     ax.set_ylabel("Training Time (s)")
     ax.legend()
     fig.tight_layout()
     fig.savefig(path, dpi=120)
+    return path
+
+
+def _plot_svg(series, path, xlabel, w=640, h=420):
+    ml, mr, mt, mb = 70, 20, 20, 50
+    xs = sorted({x for k, _ in series.values() for x in k})
+    ys = [y for _, v in series.values() for y in v]
+    if not xs or not ys:
+        return None
+    x0, x1, y1 = min(xs), max(xs), max(ys) * 1.08
+    sx = lambda x: ml + (w - ml - mr) * ((x - x0) / (x1 - x0) if x1 > x0 else 0.5)
+    sy = lambda y: h - mb - (h - mt - mb) * (y / y1 if y1 > 0 else 0.0)
+    colors = ["#1f77b4", "#ff7f0e", "#2ca02c", "#d62728", "#9467bd"]
+    o = [f'<svg xmlns="http://www.w3.org/2000/svg" width="{w}" height="{h}" font-family="sans-serif" font-size="12">',
+         f'<rect width="{w}" height="{h}" fill="white"/>',
+         f'<line x1="{ml}" y1="{h - mb}" x2="{w - mr}" y2="{h - mb}" stroke="black"/>',
+         f'<line x1="{ml}" y1="{mt}" x2="{ml}" y2="{h - mb}" stroke="black"/>']
+    for x in xs:
+        o.append(f'<text x="{sx(x):.1f}" y="{h - mb + 16}" text-anchor="middle">{x:g}</text>')
+    for i in range(6):
+        y = y1 * i / 5
+        o.append(f'<text x="{ml - 6}" y="{sy(y) + 4:.1f}" text-anchor="end">{y:.4g}</text>')
+        o.append(f'<line x1="{ml}" y1="{sy(y):.1f}" x2="{w - mr}" y2="{sy(y):.1f}" stroke="#dddddd"/>')
+    o.append(f'<text x="{(ml + w - mr) / 2}" y="{h - 10}" text-anchor="middle">{xlabel}</text>')
+    o.append(f'<text x="16" y="{(mt + h - mb) / 2}" text-anchor="middle" transform="rotate(-90 16 {(mt + h - mb) / 2})">Training Time (s)</text>')
+    for i, (tr, (k, v)) in enumerate(series.items()):
+        c = colors[i % len(colors)]
+        pts = " ".join(f"{sx(x):.1f},{sy(y):.1f}" for x, y in zip(k, v))
+        o.append(f'<polyline points="{pts}" fill="none" stroke="{c}" stroke-width="2"/>')
+        for x, y in zip(k, v):
+            o.append(f'<circle cx="{sx(x):.1f}" cy="{sy(y):.1f}" r="3.5" fill="{c}"/>')
+        o.append(f'<rect x="{w - mr - 130}" y="{mt + 18 * i}" width="12" height="12" fill="{c}"/>')
+        o.append(f'<text x="{w - mr - 112}" y="{mt + 18 * i + 11}">{tr}</text>')
+    o.append("</svg>")
+    Path(path).write_text("\n".join(o) + "\n")
+    return path
 
 
 def main():
