@@ -75,6 +75,17 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         raise RuntimeError("nvcc not found; cannot build libb200rnn.so")
     BUILD_DIR.mkdir(parents=True, exist_ok=True)
     LIB_PATH.parent.mkdir(parents=True, exist_ok=True)
+    # one builder at a time: the ranks of a launch all import the package, and concurrent nvcc runs writing the
+    # same object files corrupt each other.  The others wait for the lock and then find the library fresh.
+    import fcntl
+    with open(BUILD_DIR / ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if not force and not is_stale():
+            return LIB_PATH
+        return _build_locked(nvcc, force, verbose)
+
+
+def _build_locked(nvcc: str, force: bool, verbose: bool) -> Path:
     srcs = _sources()
     hdr_t = _headers_mtime()
     jobs = []

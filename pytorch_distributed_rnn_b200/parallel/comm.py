@@ -67,12 +67,24 @@ def make_comm(info: Optional[RankInfo] = None, prefer: Optional[str] = None):
     info = info or rank_info()
     prefer = prefer or os.environ.get("B200RNN_COMM", "auto")
     if info.world_size > 1 and info.device.type == "cuda" and prefer in ("auto", "symm"):
+        comm, err = None, None
         try:
             from .symm import SymmComm
-            return SymmComm(info)
+            comm = SymmComm(info)
         except Exception as e:  # noqa: BLE001 - report and fall back to the NCCL baseline only when allowed
-            if prefer == "symm":
-                raise
-            import logging
-            logging.warning("symmetric-memory communicator unavailable (%s); using NCCL baseline", e)
+            err = e
+        # every rank must end up with the same kind of communicator: a rank that fell back to NCCL while its peers
+        # spin in the NVLink kernels would hang the job, so the fallback is taken by all ranks or by none
+        ok = torch.tensor([1 if comm is not None else 0], device=info.device)
+        if dist.is_initialized():
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 1:
+            return comm
+        if comm is not None:
+            comm.close()
+        if prefer == "symm":
+            raise RuntimeError(f"symmetric-memory communicator unavailable on this or a peer rank: {err}")
+        import logging
+        logging.warning("symmetric-memory communicator unavailable (%s); all ranks use the NCCL baseline",
+                        err if err is not None else "a peer rank failed to set it up")
     return TorchDistComm(info)

@@ -94,11 +94,18 @@ def broadcast_optimizer_state(optimizer: torch.optim.Optimizer, root_rank: int =
 
 
 class DistributedOptimizer:
-    """Wraps any ``torch.optim.Optimizer``; averages gradients across ranks before ``step()``."""
+    """Wraps any ``torch.optim.Optimizer``; averages gradients across ranks before ``step()``.
 
-    def __init__(self, optimizer: torch.optim.Optimizer, named_parameters: Optional[Iterable[Tuple[str, torch.Tensor]]] = None):
+    ``backward_passes_per_step`` (Horovod's own knob for gradient accumulation): the fused all-reduce is launched by
+    the gradient hooks of the LAST of that many backward passes only; with the default of 1 a second ``backward()``
+    before ``step()`` is an error instead of silently re-reducing an already reduced buffer."""
+
+    def __init__(self, optimizer: torch.optim.Optimizer, named_parameters: Optional[Iterable[Tuple[str, torch.Tensor]]] = None,
+                 backward_passes_per_step: int = 1):
         self._opt = optimizer
         self._comm = _c()
+        self._passes_per_step = max(1, int(backward_passes_per_step))
+        self._passes = 0
         if named_parameters is not None:
             named = list(named_parameters)
         else:
@@ -120,9 +127,15 @@ class DistributedOptimizer:
         return getattr(self._opt, name)
 
     def _hook(self, p):
+        if not self._synced:
+            raise RuntimeError("backward() ran again after the gradients had been all-reduced and before step(): "
+                               "pass backward_passes_per_step=N to DistributedOptimizer to accumulate over N passes")
         self._ready += 1
         if self._ready == len(self._params):
-            self._launch()
+            self._ready = 0
+            self._passes += 1
+            if self._passes == self._passes_per_step:
+                self._launch()
 
     def _launch(self):
         grads = [p.grad for p in self._params if p.grad is not None]
@@ -142,8 +155,8 @@ class DistributedOptimizer:
     def synchronize(self):
         if self._comm.world == 1:
             return
-        if self._synced and self._ready < len(self._params):
-            self._launch()  # some gradients never fired (unused parameters / manual grads)
+        if self._synced:
+            self._launch()  # some gradients never fired (unused parameters / manual grads / fewer passes than announced)
         if not self._synced:
             if self._work is not None:
                 self._work.wait()
@@ -153,6 +166,7 @@ class DistributedOptimizer:
                     g.copy_(src)
             self._synced = True
         self._ready = 0
+        self._passes = 0
 
     def step(self, closure=None):
         self.synchronize()

@@ -223,14 +223,24 @@ class Trainer:
                     batch_idx=bi, batches=n_batches, training_examples=n, correct=correct, loss=loss))
             pending.clear()
 
+        # the epoch's index vector goes to the device once (27 KB for the reference's dataset); batches are slices of it
+        idx_dev, off = None, 0
+        if self.engine is not None and batches:
+            idx_dev = torch.cat(batches).to(self.device, non_blocking=True)
+        # per-step progress lines need a host read per step (the reference reads loss.item() twice per step); when
+        # they are not going to be emitted (log level above INFO) the metrics stay in the device ring until the epoch ends
+        per_step = not self.deferred_logging and logging.getLogger().isEnabledFor(logging.INFO)
         for batch_idx, idx in enumerate(batches):
             n = idx.numel()
             if self.engine is not None:
-                m = self.engine.train_step_gather(ds.features, ds.labels, idx.to(self.device, non_blocking=True))
-                pending.append((batch_idx, n, m.clone() if self.deferred_logging else m))
+                m = self.engine.train_step_gather(ds.features, ds.labels, idx_dev[off:off + n])
+                off += n
+                # a ring slot is only reused after METRIC_RING steps: no copy needed for shorter epochs
+                keep = per_step or n_batches <= getattr(self.engine, "METRIC_RING", 0)
+                pending.append((batch_idx, n, m if keep else m.clone()))
             else:
                 pending.append((batch_idx, n, self._torch_train_step(ds, idx)))
-            if not self.deferred_logging:
+            if per_step:
                 flush()
         flush()
         return total_loss / len(ds), total_correct / len(ds)
