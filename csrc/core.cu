@@ -22,19 +22,28 @@ namespace {
 __global__ void gather_kernel(const float* __restrict__ feats, const int64_t* __restrict__ labels,
                               const int64_t* __restrict__ idx, int batch, int row_elems,
                               float* __restrict__ x_out, int64_t* __restrict__ y_out) {
-  const int b = blockIdx.x;
-  if (b >= batch) return;
-  const int64_t src = idx[b];
-  const float* s = feats + src * (int64_t)row_elems;
-  float* d = x_out + (int64_t)b * row_elems;
-  if ((row_elems & 3) == 0) {
-    const float4* s4 = reinterpret_cast<const float4*>(s);
-    float4* d4 = reinterpret_cast<float4*>(d);
-    for (int i = threadIdx.x; i < row_elems / 4; i += blockDim.x) d4[i] = __ldg(&s4[i]);
-  } else {
-    for (int i = threadIdx.x; i < row_elems; i += blockDim.x) d[i] = __ldg(&s[i]);
+  // grid-stride over rows: a capped grid (b200rnn_gather_batch_capped) keeps a gather that streams from pinned
+  // host memory on a side stream from occupying the SMs the training kernels run on
+  for (int b = blockIdx.x; b < batch; b += gridDim.x) {
+    const int64_t src = idx[b];
+    const float* s = feats + src * (int64_t)row_elems;
+    float* d = x_out + (int64_t)b * row_elems;
+    if ((row_elems & 3) == 0) {
+      const float4* s4 = reinterpret_cast<const float4*>(s);
+      float4* d4 = reinterpret_cast<float4*>(d);
+      const int n4 = row_elems / 4;
+      int i = threadIdx.x;
+      for (; i + 3 * (int)blockDim.x < n4; i += 4 * blockDim.x) {   // four independent 16-byte loads in flight
+        const float4 v0 = __ldg(&s4[i]), v1 = __ldg(&s4[i + blockDim.x]);
+        const float4 v2 = __ldg(&s4[i + 2 * blockDim.x]), v3 = __ldg(&s4[i + 3 * blockDim.x]);
+        d4[i] = v0; d4[i + blockDim.x] = v1; d4[i + 2 * blockDim.x] = v2; d4[i + 3 * blockDim.x] = v3;
+      }
+      for (; i < n4; i += blockDim.x) d4[i] = __ldg(&s4[i]);
+    } else {
+      for (int i = threadIdx.x; i < row_elems; i += blockDim.x) d[i] = __ldg(&s[i]);
+    }
+    if (threadIdx.x == 0 && labels != nullptr && y_out != nullptr) y_out[b] = labels[src];
   }
-  if (threadIdx.x == 0 && labels != nullptr && y_out != nullptr) y_out[b] = labels[src];
 }
 
 // K11, time-major form: x_out[t][b][:] = feats[idx[b]][t][:] — the large-hidden path reads its input time-major
@@ -182,14 +191,21 @@ using namespace b200rnn;
 extern "C" const char* b200rnn_last_error(void) { return g_err; }
 extern "C" int b200rnn_version(void) { return 100; }
 
+extern "C" int b200rnn_gather_batch_capped(const float* feats, const int64_t* labels, const int64_t* idx,
+                                           int32_t batch, int32_t row_elems, float* x_out, int64_t* y_out,
+                                           int32_t max_blocks, void* stream) {
+  B200_REQUIRE(feats && idx && x_out && batch >= 0 && row_elems > 0, B200RNN_EINVAL, "gather_batch: bad argument");
+  if (batch == 0) return B200RNN_OK;
+  const int grid = (max_blocks > 0 && max_blocks < batch) ? max_blocks : batch;
+  gather_kernel<<<grid, 128, 0, (cudaStream_t)stream>>>(feats, labels, idx, batch, row_elems, x_out, y_out);
+  B200_CHECK_LAUNCH();
+  return B200RNN_OK;
+}
+
 extern "C" int b200rnn_gather_batch(const float* feats, const int64_t* labels, const int64_t* idx,
                                     int32_t batch, int32_t row_elems, float* x_out, int64_t* y_out,
                                     void* stream) {
-  B200_REQUIRE(feats && idx && x_out && batch >= 0 && row_elems > 0, B200RNN_EINVAL, "gather_batch: bad argument");
-  if (batch == 0) return B200RNN_OK;
-  gather_kernel<<<batch, 128, 0, (cudaStream_t)stream>>>(feats, labels, idx, batch, row_elems, x_out, y_out);
-  B200_CHECK_LAUNCH();
-  return B200RNN_OK;
+  return b200rnn_gather_batch_capped(feats, labels, idx, batch, row_elems, x_out, y_out, 0, stream);
 }
 
 extern "C" int b200rnn_gather_batch_tm(const float* feats, const int64_t* idx, int32_t batch, int32_t seq_len,

@@ -65,6 +65,12 @@ int b200rnn_version(void);
 int b200rnn_gather_batch(const float* feats, const int64_t* labels,
                          const int64_t* idx, int32_t batch, int32_t row_elems,
                          float* x_out, int64_t* y_out, void* stream);
+/* Same with at most max_blocks CTAs (0 = one per row): for a gather that streams its rows out of PINNED HOST
+ * memory on a side stream (feats / labels may be any device-accessible addresses) without taking the SMs away
+ * from the kernels it overlaps with. */
+int b200rnn_gather_batch_capped(const float* feats, const int64_t* labels,
+                                const int64_t* idx, int32_t batch, int32_t row_elems,
+                                float* x_out, int64_t* y_out, int32_t max_blocks, void* stream);
 /* Time-major form for the large-hidden path: x_tm_out[t][b][:] = feats[idx[b]][t][:] (idx nullable = identity),
  * i.e. gather and [B,T,I] -> [T,B,I] transpose in one pass. */
 int b200rnn_gather_batch_tm(const float* feats, const int64_t* idx, int32_t batch, int32_t seq_len,

@@ -78,6 +78,7 @@ def _declare(lib: C.CDLL) -> None:
     lib.b200rnn_version.restype = i32
     sigs = {
         "b200rnn_gather_batch": (i32, [vp, vp, vp, i32, i32, vp, vp, vp]),
+        "b200rnn_gather_batch_capped": (i32, [vp, vp, vp, i32, i32, vp, vp, i32, vp]),
         "b200rnn_rnn_small_supported": (i32, [P(ModelDesc)]),
         "b200rnn_rnn_small_tiling": (i32, [P(ModelDesc), P(i32), P(i32)]),
         "b200rnn_rnn_stash_floats": (i64, [P(ModelDesc)]),

@@ -157,9 +157,9 @@ def _train_steps_dataset(self, feats_pinned: torch.Tensor, labels_pinned: torch.
             idx_pin[i].copy_(idx)
             idx_dev[i].copy_(idx_pin[i], non_blocking=True)
             # the GPU pulls the batch's rows out of the pinned dataset itself (peer reads over PCIe)
-            _native.check(lib.b200rnn_gather_batch(feats_pinned.data_ptr(), labels_flat.data_ptr(), idx_dev[i].data_ptr(), B,
-                                                   T * I, slots[i][0].data_ptr(), slots[i][1].data_ptr(), cs.cuda_stream),
-                          "gather_batch")
+            _native.check(lib.b200rnn_gather_batch_capped(feats_pinned.data_ptr(), labels_flat.data_ptr(), idx_dev[i].data_ptr(), B,
+                                                          T * I, slots[i][0].data_ptr(), slots[i][1].data_ptr(), 64,
+                                                          cs.cuda_stream), "gather_batch")   # PCIe-bound: 64 CTAs saturate it
             copied[i].record(cs)
 
     it = iter(index_batches)
