@@ -292,9 +292,17 @@ extern "C" int b200rnn_wave_status_lstm_bwd_dx(void);
 extern "C" int b200rnn_wave_status_gru_fwd(void);
 extern "C" int b200rnn_wave_status_gru_bwd(void);
 extern "C" int b200rnn_wave_status_gru_bwd_dx(void);
+extern "C" int b200rnn_wave_status_lstm_fwd_h16(void);
+extern "C" int b200rnn_wave_status_lstm_bwd_h16(void);
+extern "C" int b200rnn_wave_status_lstm_bwd_dx_h16(void);
+extern "C" int b200rnn_wave_status_gru_fwd_h16(void);
+extern "C" int b200rnn_wave_status_gru_bwd_h16(void);
+extern "C" int b200rnn_wave_status_gru_bwd_dx_h16(void);
 extern "C" int b200rnn_wave_status(int32_t* status) {
   B200_REQUIRE(status != nullptr, B200RNN_EINVAL, "wave_status: null");
   *status = b200rnn_wave_status_lstm_fwd() | b200rnn_wave_status_lstm_bwd() | b200rnn_wave_status_lstm_bwd_dx() |
-            b200rnn_wave_status_gru_fwd() | b200rnn_wave_status_gru_bwd() | b200rnn_wave_status_gru_bwd_dx();
+            b200rnn_wave_status_gru_fwd() | b200rnn_wave_status_gru_bwd() | b200rnn_wave_status_gru_bwd_dx() |
+            b200rnn_wave_status_lstm_fwd_h16() | b200rnn_wave_status_lstm_bwd_h16() | b200rnn_wave_status_lstm_bwd_dx_h16() |
+            b200rnn_wave_status_gru_fwd_h16() | b200rnn_wave_status_gru_bwd_h16() | b200rnn_wave_status_gru_bwd_dx_h16();
   return B200RNN_OK;
 }

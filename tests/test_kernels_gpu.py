@@ -207,3 +207,51 @@ def test_tensor_core_forward_matches_torch_and_ffma(B, T, I, L):
     out_tc = s_tc[:L * T * B * 32].view(L, T, B, 32)[L - 1].permute(1, 0, 2).cpu()
     assert torch.allclose(out_tc, ro, atol=3e-5, rtol=1e-4), float((out_tc - ro).abs().max())
     assert torch.allclose(s_tc, s_ff, atol=3e-5, rtol=1e-4), float((s_tc - s_ff).abs().max())
+
+
+# ---- hidden size 16 (the other member of the small-hidden fused family; `--hidden-units 16`) ----
+@pytest.mark.parametrize("cell,B,T,I,L", [("lstm", 37, 16, 9, 2), ("lstm", 1440, 12, 9, 2), ("lstm", 19, 9, 24, 3),
+                                          ("gru", 50, 21, 9, 2), ("gru", 6, 5, 30, 1)])
+def test_hidden16_forward_and_backward_match_torch(cell, B, T, I, L):
+    from pytorch_distributed_rnn_b200 import FusedGRU
+    torch.manual_seed(3 * B + L)
+    m = (FusedLSTM if cell == "lstm" else FusedGRU)(I, 16, L, batch_first=True).to(DEV)
+    ref = (nn.LSTM if cell == "lstm" else nn.GRU)(I, 16, L, batch_first=True)
+    ref.load_state_dict({k: v.detach().cpu() for k, v in m.state_dict().items()})
+    x = torch.randn(B, T, I)
+    wo, wh = torch.randn(B, T, 16), torch.randn(L, B, 16)
+    out, hx = m(x.to(DEV))
+    ro, rhx = ref(x)
+    h, rh = (hx[0], rhx[0]) if cell == "lstm" else (hx, rhx)
+    assert torch.allclose(out.detach().cpu(), ro.detach(), atol=2e-5, rtol=1e-4), float((out.detach().cpu() - ro).abs().max())
+    ((out * wo.to(DEV)).sum() + (h * wh.to(DEV)).sum()).backward()
+    ((ro * wo).sum() + (rh * wh).sum()).backward()
+    for (n, p), q in zip(m.named_parameters(), ref.parameters()):
+        err = float((p.grad.cpu() - q.grad).abs().max())
+        scale = float(q.grad.abs().max()) + 1e-6
+        assert err <= 2e-4 * scale + 2e-5, (n, err, scale)
+    _native.assert_device_healthy()
+
+
+@pytest.mark.parametrize("B,T,L,cell", [(96, 32, 2, "lstm"), (180, 24, 2, "lstm"), (50, 10, 1, "gru")])
+def test_engine_hidden16_train_steps_match_torch_adam(B, T, L, cell):
+    torch.manual_seed(B + 16)
+    steps, lr, N = 4, 0.0025, 2 * B + 3
+    model = MotionModel(9, 16, L, 6, cell=cell)
+    ref = copy.deepcopy(model)
+    feats, labels = torch.randn(N, T, 9), torch.randint(0, 6, (N, 1))
+    idxs = [torch.randperm(N)[:B] for _ in range(steps)]
+    want = _ref_train(ref, [feats[i] for i in idxs], [labels[i].view(-1) for i in idxs], lr, steps)
+    model = model.to(DEV)
+    eng = FusedTrainEngine(model, lr=lr)                 # the 3-launch engine, not the composite fallback
+    fd, ld = feats.to(DEV), labels.to(DEV)
+    got = []
+    for s in range(steps):
+        m = eng.train_step_gather(fd, ld, idxs[s].to(DEV)).cpu()
+        got.append((float(m[0]) / B, int(round(float(m[1])))))
+    _native.assert_device_healthy()
+    for (gl, gc), (wl, wc) in zip(got, want):
+        assert abs(gl - wl) < 2e-5, (got, want)
+        assert abs(gc - wc) <= max(1, B // 500), (got, want)
+    for (n, p), q in zip(model.named_parameters(), ref.parameters()):
+        assert torch.allclose(p.detach().cpu(), q.detach(), atol=5e-5), (n, float((p.detach().cpu() - q).abs().max()))
