@@ -52,6 +52,11 @@ def ensure_reference(wait_s: float = 120.0) -> str:
         return "already installed"
     lock = HERE / "_ref.lock"
     try:
+        if lock.exists() and time.time() - lock.stat().st_mtime > 600:
+            lock.rmdir()      # left behind by an installer that died: nobody installs for ten minutes
+    except OSError:
+        pass
+    try:
         lock.mkdir()
     except FileExistsError:
         deadline = time.time() + wait_s

@@ -193,6 +193,9 @@ class Trainer:
         if self.device.type == "cuda":
             from .. import _native
             _native.assert_device_healthy()
+        status = getattr(self.engine, "reducer_status", None)
+        if status is not None and status() != 0:
+            raise RuntimeError(f"gradient reducer: a bucket's device-side trigger wait timed out (status {status():#x})")
 
     def _epoch_barrier(self) -> None:
         """Hook: distributed trainers wait here for rank 0's validation / checkpoint of this epoch."""
