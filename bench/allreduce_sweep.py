@@ -42,7 +42,7 @@ ALGOS = ((4, "ll"), (1, "oneshot"), (2, "twoshot"), (3, "nvls"))
 
 def crossovers(rows):
     """Measured crossovers (bytes) between the variants for one world size, rows sorted by size, delay 0."""
-    rows = sorted((r for r in rows if r["delay_us"] == 0), key=lambda r: r["bytes"])
+    rows = sorted((r for r in rows if r["delay_us"] == 0 and not r.get("loss_pct")), key=lambda r: r["bytes"])
     ll_max, one_max, nvls_min = 0, 0, None
     for r in rows:
         if "oneshot_us" in r and "twoshot_us" in r and r["oneshot_us"] <= r["twoshot_us"]:
@@ -68,7 +68,7 @@ def write_md(path, results, world):
              "| bytes | rows | LL | one-shot | two-shot | NVLS | NCCL all_reduce | best own / NCCL | best-own frac of roofline @770 | @900 |",
              "|---|---|---|---|---|---|---|---|---|---|"]
     for r in results:
-        if r["delay_us"] != 0:
+        if r["delay_us"] != 0 or r.get("loss_pct"):
             continue
         ours = {k: r[f"{k}_us"] for _, k in ALGOS if f"{k}_us" in r}
         best = min(ours, key=ours.get)
@@ -83,6 +83,13 @@ def write_md(path, results, world):
         for r in delayed:
             f = lambda k: f"{r[k + '_us']:.1f}" if k + "_us" in r else "-"
             lines.append(f"| {r['delay_us']} | {r['bytes']} | {f('ll')} | {f('oneshot')} | {f('twoshot')} | {f('nvls')} |")
+    lossy = [r for r in results if r.get("loss_pct")]
+    if lossy:
+        lines += ["", "## Injected message loss (a dropped publication pays a 200 us retransmission timeout)", "",
+                  "| loss % | bytes | LL | one-shot | two-shot | NVLS |", "|---|---|---|---|---|---|"]
+        for r in lossy:
+            f = lambda k: f"{r[k + '_us']:.1f}" if k + "_us" in r else "-"
+            lines.append(f"| {r['loss_pct']} | {r['bytes']} | {f('ll')} | {f('oneshot')} | {f('twoshot')} | {f('nvls')} |")
     Path(path).write_text("\n".join(lines) + "\n")
 
 
@@ -113,6 +120,7 @@ def main():
     ap.add_argument("--min-bytes", type=int, default=4 << 10)
     ap.add_argument("--max-bytes", type=int, default=256 << 20)
     ap.add_argument("--delay-us", type=str, default="0", help="comma list of injected delays (us)")
+    ap.add_argument("--loss-pct", type=str, default="", help="comma list of injected message-loss percentages (run after the delays)")
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--rows", type=int, default=1, help="local gradient rows to reduce inside the call (the fused step has ~90-144)")
     ap.add_argument("--out", default=None)
@@ -134,8 +142,10 @@ def main():
         sizes.append(b)
         b *= 4
     sizes = sorted(set(sizes + [int(x) for x in a.extra_bytes.split(",") if x and a.min_bytes <= int(x) <= a.max_bytes]))
-    for delay in [int(x) for x in a.delay_us.split(",")]:
+    rules = [(int(x), 0.0) for x in a.delay_us.split(",")] + [(0, float(x)) for x in a.loss_pct.split(",") if x]
+    for delay, loss in rules:
         comm.set_delay_ns(delay * 1000)
+        comm.set_loss(loss)
         for nbytes in sizes:
             n = nbytes // 4
             # the vector lives in the symmetric heap (needed by two-shot's parameter all-gather)
@@ -144,7 +154,7 @@ def main():
             opt = FusedSGD(arena, lr=0.0)
             rows = torch.ones(a.rows, n + 2, device=dev)
             slot = torch.zeros(2, device=dev)
-            row = {"bytes": nbytes, "world": world, "delay_us": delay, "rows": a.rows}
+            row = {"bytes": nbytes, "world": world, "delay_us": delay, "loss_pct": loss, "rows": a.rows}
             for algo, name in ALGOS:
                 if algo == 3 and comm.mc_base is None:
                     continue
@@ -159,7 +169,7 @@ def main():
                     comm.allreduce_update(rows, a.rows, arena, opt, opt.desc(grad_scale=1.0 / world), slot)
                 row[f"{name}_us"] = timed(fn, a.iters, 5, dev)
             comm.algo = 0
-            if delay == 0:
+            if delay == 0 and loss == 0:
                 t = torch.ones(n, device=dev)
                 row["nccl_us"] = timed(lambda: dist.all_reduce(t), a.iters, 5, dev)
             per_rank_one = (world - 1) * nbytes

@@ -49,13 +49,15 @@ def load(files):
     return rows
 
 
-def table(rows, network=False):
+def table(rows, network=False, rule="delay"):
+    if network:
+        rows = [r for r in rows if (r.get("rule_type") or "delay") == rule]
     key = (lambda r: (r["trainer"], r["rule_value"])) if network else (lambda r: (r["trainer"], r["ranks"], r["batch"]))
     groups = defaultdict(list)
     for r in rows:
         groups[key(r)].append(r)
     out = []
-    head = "| trainer | delay us | s | samples/s | n |" if network else "| trainer | ranks | batch | s | samples/s | MiB | n |"
+    head = f"| trainer | {'loss %' if rule == 'loss' else 'delay us'} | s | samples/s | n |" if network else "| trainer | ranks | batch | s | samples/s | MiB | n |"
     out.append(head)
     out.append("|" + "---|" * (head.count("|") - 1))
     for k in sorted(groups, key=lambda x: tuple(str(v) if v is None else v for v in x)):
@@ -83,11 +85,13 @@ def _series(rows, network):
     return out
 
 
-def plot(rows, path, network=False):
+def plot(rows, path, network=False, rule="delay"):
     """Training time vs ranks (or injected delay) per trainer.  matplotlib (Agg) when it is installed, else a
     dependency-free SVG with the same content (``path`` then gets the .svg suffix); returns the file written."""
+    if network:
+        rows = [r for r in rows if (r.get("rule_type") or "delay") == rule]
     series = _series(rows, network)
-    xlabel = "injected delay (us)" if network else "ranks (GPUs)"
+    xlabel = ("injected loss (%)" if rule == "loss" else "injected delay (us)") if network else "ranks (GPUs)"
     try:
         import matplotlib
         matplotlib.use("Agg")
@@ -145,11 +149,13 @@ def main():
     ap.add_argument("files", nargs="+")
     ap.add_argument("--plot", default=None)
     ap.add_argument("--network", action="store_true")
+    ap.add_argument("--rule", default="delay", choices=["delay", "loss"],
+                    help="--network: which rule type to tabulate (Experiments_network.ipynb plots both)")
     a = ap.parse_args()
     rows = load(a.files)
-    print(table(rows, a.network))
+    print(table(rows, a.network, a.rule))
     if a.plot:
-        plot(rows, a.plot, a.network)
+        plot(rows, a.plot, a.network, a.rule)
 
 
 if __name__ == "__main__":

@@ -33,6 +33,7 @@ ROOT = Path(__file__).resolve().parent.parent
 BATCH_SIZES = [480, 960, 1440]
 TRAINERS = ["local", "distributed", "horovod"]
 DELAYS_US = [0, 1, 2, 5, 10, 25, 50, 100, 200, 300, 400]   # the reference's delay list, ms -> us (NVLink scale)
+LOSSES_PCT = [0, 0.1, 0.5, 1, 2, 5, 10, 15]                 # the reference's loss list (fabfile.py:149-151 and results)
 
 
 def train_runs(ranks, repeats):
@@ -130,7 +131,7 @@ def run_packed(runs, dataset_path, results_file, n_gpus, env=None, tag=None):
 
 def tag_fields(tag):
     kind, value = tag.split("=")
-    return {"rule_type": kind, "rule_value": float(value), "rule": f"{kind} {value}us"}
+    return {"rule_type": kind, "rule_value": float(value), "rule": f"{kind} {value}{'%' if kind == 'loss' else 'us'}"}
 
 
 def main():
@@ -142,6 +143,7 @@ def main():
     ap.add_argument("--network", action="store_true", help="delay-injection experiment instead of the scaling grid")
     ap.add_argument("--pack", type=int, default=0, help="GPUs of the box: run smaller worlds side by side on disjoint GPUs")
     ap.add_argument("--delays", default=",".join(map(str, DELAYS_US)), help="--network: injected delays in us")
+    ap.add_argument("--losses", default=",".join(map(str, LOSSES_PCT)), help="--network: injected message loss in percent")
     a = ap.parse_args()
     ranks = [int(x) for x in a.ranks.split(",")]
     # one dataset for the whole experiment, written before anything runs (runs may start side by side)
@@ -159,15 +161,28 @@ def main():
     run_network(a, n)
 
 
-def run_network(a, n):
-    """O2: the delay experiment.  One job per trainer sweeps all delays in-process (`--delay-sweep-us`: start-up costs
-    seconds, an epoch milliseconds); its log is split at the delay markers into one result entry per (trainer, delay),
-    in the reference's network-results schema."""
+def split_network_log(log):
+    """{(rule_type, value string): log text} from a `--delay-sweep-us` / `--loss-sweep-pct` job's stderr: every rank's
+    log contributes one segment per rule, behind its `Injected delay: N us` / `Injected loss: P %` marker."""
     import re
+    parts = re.split(r"^.*Injected (delay|loss): ([0-9.]+) (?:us|%).*$", log, flags=re.M)
+    by_rule = {}
+    for kind, value, text in zip(parts[1::3], parts[2::3], parts[3::3]):
+        by_rule[(kind, value)] = by_rule.get((kind, value), "") + text
+    return by_rule
+
+
+def run_network(a, n):
+    """O2: the delay / loss experiment.  One job per trainer sweeps all rules in-process (`--delay-sweep-us`,
+    `--loss-sweep-pct`: start-up costs seconds, an epoch milliseconds); its log is split at the rule markers into one
+    result entry per (trainer, rule), in the reference's network-results schema."""
     for tr in ("distributed", "horovod"):
-        run = {"trainer": tr, "hosts": n, "slots": 1, "repeat": 0,
-               "parameters": {"--batch-size": 1440, "--epochs": 1, "--seed": 123456789, "--no-validation": "",
-                              "--delay-sweep-us": a.delays}}
+        params = {"--batch-size": 1440, "--epochs": 1, "--seed": 123456789, "--no-validation": ""}
+        if a.delays:
+            params["--delay-sweep-us"] = a.delays
+        if a.losses:
+            params["--loss-sweep-pct"] = a.losses
+        run = {"trainer": tr, "hosts": n, "slots": 1, "repeat": 0, "parameters": params}
         cmd = get_command(run, a.dataset_path)
         command = " ".join(cmd)
         results = load_results(a.results)
@@ -176,17 +191,13 @@ def run_network(a, n):
             continue
         print(command, flush=True)
         cp = subprocess.run(cmd, capture_output=True, text=True, env=dict(os.environ, PYTHONPATH=str(ROOT)), cwd=str(ROOT))
-        parts = re.split(r"^.*Injected delay: (\d+) us.*$", cp.stderr, flags=re.M)
-        # parts = [preamble, d0, log0, d1, log1, ...] with every rank's log contributing one segment per delay
-        by_delay = {}
-        for d, log in zip(parts[1::2], parts[2::2]):
-            by_delay[d] = by_delay.get(d, "") + log
-        for d, log in by_delay.items():
-            entry = {"command": f"{command}  #delay={d}", "sweep_command": command, "trainer": tr, "stdout": "", "stderr": log,
+        by_rule = split_network_log(cp.stderr)
+        for (kind, value), log in by_rule.items():
+            entry = {"command": f"{command}  #{kind}={value}", "sweep_command": command, "trainer": tr, "stdout": "", "stderr": log,
                      "returncode": cp.returncode, "config": {k: run[k] for k in ("trainer", "hosts", "slots", "parameters")}}
-            entry.update(tag_fields(f"delay={d}"))
+            entry.update(tag_fields(f"{kind}={value}"))
             results.append(entry)
-        if len(parts) < 3:   # the job failed before the first marker: record it as the reference records failed runs
+        if not by_rule:   # the job failed before the first marker: record it as the reference records failed runs
             results.append({"command": command, "sweep_command": command, "trainer": tr, "stdout": cp.stdout, "stderr": cp.stderr,
                             "returncode": cp.returncode, "config": {k: run[k] for k in ("trainer", "hosts", "slots", "parameters")}})
         with open(a.results, "w") as f:

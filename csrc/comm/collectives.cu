@@ -45,7 +45,7 @@ long long default_timeout_cycles() {
 }
 
 struct Ctx {  // device-side view
-  int rank, world, max_blocks, delay_ns;
+  int rank, world, max_blocks, delay_ns, loss_ppm, loss_rto_ns;
   long long inbox_floats, timeout, ll_floats;
   char* base[B200RNN_MAX_PEERS];
   long long off_flags_ar, off_flags_pr, off_flags_sig, off_flags_bar, off_status, off_inbox, off_heap, off_ll;
@@ -54,6 +54,7 @@ struct Ctx {  // device-side view
 Ctx to_dev(const b200rnn_comm_ctx* c) {
   Ctx d;
   d.rank = c->rank; d.world = c->world; d.max_blocks = c->max_blocks; d.delay_ns = c->delay_ns;
+  d.loss_ppm = c->loss_ppm; d.loss_rto_ns = c->loss_rto_ns > 0 ? c->loss_rto_ns : 200000;
   d.inbox_floats = c->inbox_floats;
   d.timeout = c->timeout_cycles > 0 ? c->timeout_cycles : default_timeout_cycles();
   d.ll_floats = c->ll_floats; d.off_ll = c->off_ll;
@@ -84,11 +85,28 @@ __device__ __forceinline__ uint32_t* flags_pr(const Ctx& c, int owner, int blk) 
 __device__ __forceinline__ float* inbox(const Ctx& c, int owner, uint32_t seq, int src) {
   return reinterpret_cast<float*>(c.base[owner] + c.off_inbox) + ((long long)(seq & 1) * c.world + src) * c.inbox_floats;
 }
-__device__ __forceinline__ void delay(const Ctx& c) {
-  if (c.delay_ns > 0) {
-    long long t0 = clock64();
-    const long long cycles = (long long)c.delay_ns * 2;  // ~2 GHz SM clock
-    while (clock64() - t0 < cycles) { }
+// Network fault injection in front of a publication (the reference's `tc netem delay` / `tc netem loss` rules,
+// fabfile.py:146-152, at NVLink scale).  delay_ns lengthens every message.  loss_ppm "drops" a block's message with
+// that probability (a hash of seq, rank and block: the same on every run, different per message); a dropped message
+// costs one retransmission timeout loss_rto_ns and may be dropped again, up to 8 times in a row - what a lossy link
+// does to a reliable transport.  Nothing is ever really lost: the stores go out after the penalty.
+__device__ __forceinline__ uint32_t mix32(uint32_t h) {
+  h ^= h >> 16; h *= 0x85EBCA6Bu; h ^= h >> 13; h *= 0xC2B2AE35u; h ^= h >> 16;
+  return h;
+}
+__device__ __forceinline__ void spin_ns(long long ns) {
+  const long long t0 = clock64();
+  const long long cycles = ns * 2;  // ~2 GHz SM clock
+  while (clock64() - t0 < cycles) { }
+}
+__device__ __forceinline__ void delay(const Ctx& c, uint32_t seq) {
+  if (c.delay_ns > 0) spin_ns(c.delay_ns);
+  if (c.loss_ppm > 0) {
+    uint32_t h = mix32(seq * 0x9E3779B1u ^ mix32((uint32_t)c.rank * 0x01000193u + blockIdx.x + 0x5BD1E995u));
+    for (int tries = 0; tries < 8 && (int)(h % 1000000u) < c.loss_ppm; ++tries) {
+      spin_ns(c.loss_rto_ns);
+      h = mix32(h + 0x9E3779B9u);
+    }
   }
 }
 // Spin until *f >= seq (wrap-safe); on timeout set bit `src` in this rank's status word.
@@ -170,7 +188,7 @@ __global__ void __launch_bounds__(kThreads) oneshot_kernel(
   // ONE system fence (issued by the W publishing lanes together, after the barrier made every thread's peer
   // stores visible to them), then the W flags go out in parallel as relaxed stores.
   if (threadIdx.x < c.world) {
-    if (threadIdx.x == 0) delay(c);
+    if (threadIdx.x == 0) delay(c, seq);
     __syncwarp(__activemask());
     asm volatile("fence.acq_rel.sys;" ::: "memory");
     st_relaxed_sys(flags_ar(c, threadIdx.x, c.rank, blockIdx.x), seq);
@@ -247,7 +265,7 @@ __global__ void __launch_bounds__(kRowThreads) oneshot_ll_kernel(
   }
   // ---- phase 1: push (data, seq) words into every peer's LL inbox: warp `grp` serves peers grp, grp+8 ----
   if (e0 < n) {
-    delay(c);
+    delay(c, seq);
     for (int p = grp; p < c.world; p += kRG) {
       uint4* dst = ll_slot(c, p, seq, c.rank) + 2 * col4;
       st_ll(dst, mine.x, mine.y, seq);
@@ -358,7 +376,7 @@ __global__ void __launch_bounds__(kThreads) twoshot_kernel(
   }
   grid_sync(c, counter, sync_target - gridDim.x);
   if (threadIdx.x == 0 && blockIdx.x < c.world) {
-    delay(c);
+    delay(c, seq);
     st_release_sys(flags_ar(c, blockIdx.x, c.rank, 0), seq);
   }
   // ---- phase 2: owner reduces its shard, applies the optimizer, broadcasts the new parameters ----
@@ -470,7 +488,7 @@ __global__ void __launch_bounds__(kThreads) nvls_update_kernel(
   }
   asm volatile("fence.proxy.alias;" ::: "memory");
   grid_sync(c, counter, sync_target - gridDim.x);
-  if (blockIdx.x == 0 && threadIdx.x == 0) delay(c);
+  if (blockIdx.x == 0 && threadIdx.x == 0) delay(c, seq);
   rank_barrier(c, seq, false);
   asm volatile("fence.proxy.alias;" ::: "memory");
   // ---- phase 1: my shard: in-switch reduction, optimizer, in-switch broadcast of the parameters ----
@@ -546,7 +564,7 @@ __global__ void __launch_bounds__(kThreads) broadcast_kernel(Ctx c, uint32_t seq
     __syncthreads();
     if (last && threadIdx.x == 0) {
       __threadfence_system();
-      delay(c);
+      delay(c, seq);
       for (int p = 0; p < c.world; ++p)
         if (p != root) st_release_sys(reinterpret_cast<uint32_t*>(c.base[p] + c.off_flags_bar) + B200RNN_MAX_PEERS + root, seq);
     }
@@ -569,7 +587,7 @@ __global__ void __launch_bounds__(kThreads) put_kernel(Ctx c, uint32_t seq, int 
   __threadfence_system();
   __syncthreads();
   if (threadIdx.x == 0) {
-    delay(c);
+    delay(c, seq);
     st_release_sys(reinterpret_cast<uint32_t*>(c.base[dst] + c.off_flags_sig) + c.rank, seq);
   }
 }

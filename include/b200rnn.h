@@ -419,6 +419,9 @@ typedef struct {
   int64_t heap_bytes;
   int64_t ll_floats;        /* capacity (floats, per (parity, source)) of the low-latency one-shot inbox;
                                0 = default (64 Ki floats) */
+  int32_t loss_ppm;         /* injected message loss, parts per million: a block's publication is "dropped" with this
+                               probability and then costs loss_rto_ns per retransmission (tc netem loss analogue) */
+  int32_t loss_rto_ns;      /* retransmission timeout charged per dropped message (0 = 200 000 ns) */
   /* byte offsets inside a region (identical on every rank) */
   int64_t off_flags_ar, off_flags_pr, off_flags_sig, off_flags_bar, off_status, off_inbox, off_heap, off_ll;
   void* base[B200RNN_MAX_PEERS];

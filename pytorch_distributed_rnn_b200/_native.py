@@ -47,7 +47,7 @@ class CommCtx(C.Structure):
     _fields_ = [
         ("rank", C.c_int32), ("world", C.c_int32), ("max_blocks", C.c_int32), ("delay_ns", C.c_int32),
         ("inbox_floats", C.c_int64), ("timeout_cycles", C.c_int64), ("heap_bytes", C.c_int64),
-        ("ll_floats", C.c_int64),
+        ("ll_floats", C.c_int64), ("loss_ppm", C.c_int32), ("loss_rto_ns", C.c_int32),
         ("off_flags_ar", C.c_int64), ("off_flags_pr", C.c_int64), ("off_flags_sig", C.c_int64),
         ("off_flags_bar", C.c_int64), ("off_status", C.c_int64), ("off_inbox", C.c_int64), ("off_heap", C.c_int64),
         ("off_ll", C.c_int64),

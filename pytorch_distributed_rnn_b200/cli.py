@@ -53,6 +53,10 @@ EXTENSION_FLAGS = (
                             help="network experiment in one process: comma list of delays (us) injected before every flag "
                                  "publication of the in-kernel collectives; the run is repeated once per value after an "
                                  "untimed warm-up, each with its own performance line (fabfile.py:130-191 ran one job per rule)")),
+    ("loss-sweep-pct", dict(default=None, type=str,
+                            help="same experiment for message loss: comma list of percentages; a publication is dropped "
+                                 "with that probability and pays a retransmission timeout (B200RNN_LOSS_RTO_NS, default "
+                                 "200 us) before it goes out (the reference's `tc netem loss N%%` rule)")),
 )
 
 

@@ -78,7 +78,7 @@ def main(argv=None) -> int:
     while i < len(argv):  # own flags come first; everything from the script / module on is passed through
         a = argv[i]
         if a in ("-n", "--nproc"):
-            n = int(argv[i + 1]); i += 2
+            n = None if argv[i + 1] == "auto" else int(argv[i + 1]); i += 2   # auto: one rank per visible GPU
         elif a == "--timeout":
             timeout = float(argv[i + 1]); i += 2
         elif a == "-m":

@@ -109,6 +109,8 @@ class SymmComm:
         # watchdog of the in-kernel waits: B200RNN_COMM_TIMEOUT_MS (default 60 s, resolved natively when 0 here)
         ctx.inbox_floats, ctx.timeout_cycles, ctx.heap_bytes = inbox_floats, 0, heap_bytes
         ctx.ll_floats = int(os.environ.get("B200RNN_LL_FLOATS", 256 << 10))   # LL one-shot up to 1 MiB vectors
+        ctx.loss_ppm = int(os.environ.get("B200RNN_LOSS_PPM", "0"))
+        ctx.loss_rto_ns = int(os.environ.get("B200RNN_LOSS_RTO_NS", "0"))     # 0: the native default, 200 us
         region = self.lib.b200rnn_comm_layout(C.byref(ctx))
         if region <= 0:
             raise _native.NativeError("comm_layout failed")
@@ -356,6 +358,14 @@ class SymmComm:
 
     def set_delay_ns(self, ns: int) -> None:
         self.ctx.delay_ns = int(ns)
+
+    def set_loss(self, percent: float, rto_ns: int = 0) -> None:
+        """Injected message loss (the reference's `tc netem loss N%`, fabfile.py:149-151): every block's publication is
+        "dropped" with this probability and then pays `rto_ns` (0 = 200 us) per retransmission before it goes out."""
+        if not 0.0 <= percent <= 100.0:
+            raise ValueError("loss percentage must be within [0, 100]")
+        self.ctx.loss_ppm = int(round(percent * 10000))
+        self.ctx.loss_rto_ns = int(rto_ns)
 
     def close(self) -> None:
         if self.symm:

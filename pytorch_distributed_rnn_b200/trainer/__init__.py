@@ -59,28 +59,41 @@ def _write_history(args, train_history, validation_history) -> None:
 
 
 DELAY_MARK = "Injected delay: {} us"      # bench/sweep.py splits a sweep's log at these lines
+LOSS_MARK = "Injected loss: {} %"
 
 
-def _delay_sweep(args, trainer, delays_us):
-    """The reference's network experiment (tc netem delay on every host, one job per rule: fabfile.py:130-191) as
-    ONE job: after an untimed warm-up run (first-use costs: module load, buffer allocation), the same
-    ``--epochs`` training is repeated once per injected delay; every repetition logs the usual performance line
-    behind a ``Injected delay: N us`` marker.  The delay is spun on the device in front of every flag publication
-    of the in-kernel collectives (`SymmComm.set_delay_ns`), i.e. it lengthens every message's latency."""
+def _network_sweep(args, trainer, delays_us=(), losses_pct=()):
+    """The reference's network experiment (tc netem delay / loss on every host, one job per rule:
+    fabfile.py:130-191) as ONE job: after an untimed warm-up run (first-use costs: module load, buffer
+    allocation), the same ``--epochs`` training is repeated once per injected rule; every repetition logs the
+    usual performance line behind a ``Injected delay: N us`` / ``Injected loss: P %`` marker.  A delay is spun
+    on the device in front of every flag publication of the in-kernel collectives (`SymmComm.set_delay_ns`),
+    i.e. it lengthens every message's latency; a loss makes that publication pay a retransmission timeout with
+    the given probability (`SymmComm.set_loss`)."""
     comm = trainer._get_comm()
     if comm is None or not hasattr(comm, "set_delay_ns"):
-        raise SystemExit("--delay-sweep-us needs the in-kernel NVLink communicator (a multi-GPU distributed / horovod run)")
+        raise SystemExit("--delay-sweep-us / --loss-sweep-pct need the in-kernel NVLink communicator "
+                         "(a multi-GPU distributed / horovod run)")
     level = logging.getLogger().level
     logging.getLogger().setLevel(logging.WARNING)
     trainer.train(epochs=args.epochs)                       # warm-up, not reported
     logging.getLogger().setLevel(level)
-    for d in delays_us:
-        comm.set_delay_ns(d * 1000)
-        logging.info(DELAY_MARK.format(d))      # on every rank: each rank's log is split at its own markers
+    rules = [(DELAY_MARK, d, lambda v: comm.set_delay_ns(v * 1000)) for d in delays_us]
+    rules += [(LOSS_MARK, p, lambda v: comm.set_loss(v)) for p in losses_pct]
+    for mark, value, apply in rules:
+        comm.set_delay_ns(0)
+        comm.set_loss(0.0)
+        apply(value)
+        logging.info(mark.format(value))        # on every rank: each rank's log is split at its own markers
         trainer.start_epoch = 0
         trainer.train(epochs=args.epochs)
     comm.set_delay_ns(0)
+    comm.set_loss(0.0)
     return trainer
+
+
+def _delay_sweep(args, trainer, delays_us):
+    return _network_sweep(args, trainer, delays_us=delays_us)
 
 
 def train(args, trainer_cls):
@@ -93,9 +106,10 @@ def train(args, trainer_cls):
     trainer = trainer_cls(model=net, training_set=train_ds, validation_set=val_ds, test_set=test_ds,
                           batch_size=args.batch_size, learning_rate=args.learning_rate,
                           checkpoint_dir=args.checkpoint_directory, **extras)
-    sweep = getattr(args, "delay_sweep_us", None)
-    if sweep:
-        return _delay_sweep(args, trainer, [int(v) for v in str(sweep).split(",") if v != ""])
+    delays = [int(v) for v in str(getattr(args, "delay_sweep_us", None) or "").split(",") if v != ""]
+    losses = [float(v) for v in str(getattr(args, "loss_sweep_pct", None) or "").split(",") if v != ""]
+    if delays or losses:
+        return _network_sweep(args, trainer, delays_us=delays, losses_pct=losses)
     logging.info(f"Training model for {args.epochs} epochs...")
     _, train_history, validation_history = trainer.train(epochs=args.epochs)
     if getattr(trainer, "rank", 0) == 0:

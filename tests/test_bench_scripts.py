@@ -52,3 +52,49 @@ def test_analysis_parses_reference_schema_and_takes_max_over_ranks(tmp_path):
     ref = Path("/root/reference/evaluation/results_202007141730.json")
     if ref.exists():   # the reference's own result files parse too
         assert len(analysis.load([ref])) > 20
+
+
+def test_network_log_split_and_loss_rule_tables(tmp_path):
+    """O2 (fabfile.py:146-191): one sweep job's log becomes one result entry per (trainer, rule); analysis tabulates
+    delay and loss rules separately, as Experiments_network.ipynb plots them."""
+    import analysis
+    import sweep
+    log = ("INFO:root:Training set of size 6912\n"
+           "INFO:root:Injected delay: 0 us\nINFO:root:0: Memory Usage: 900.0, Training Duration: 0.010\n"
+           "INFO:root:Injected delay: 25 us\nINFO:root:0: Memory Usage: 900.0, Training Duration: 0.020\n"
+           "INFO:root:Injected loss: 0.5 %\nINFO:root:0: Memory Usage: 900.0, Training Duration: 0.030\n"
+           "INFO:root:Injected delay: 25 us\nINFO:root:1: Memory Usage: 901.0, Training Duration: 0.025\n")
+    parts = sweep.split_network_log(log)
+    assert set(parts) == {("delay", "0"), ("delay", "25"), ("loss", "0.5")}
+    assert parts[("delay", "25")].count("Training Duration") == 2            # both ranks' segments of the same rule
+    assert sweep.tag_fields("loss=0.5") == {"rule_type": "loss", "rule_value": 0.5, "rule": "loss 0.5%"}
+    assert sweep.LOSSES_PCT == [0, 0.1, 0.5, 1, 2, 5, 10, 15] and sweep.DELAYS_US[-1] == 400
+    cfg = {"trainer": "distributed", "hosts": 8, "slots": 1, "parameters": {"--batch-size": 1440}}
+    results = [dict(command=f"c #{k}={v}", stdout="", stderr=text, config=cfg, **sweep.tag_fields(f"{k}={v}"))
+               for (k, v), text in parts.items()]
+    f = tmp_path / "n.json"
+    json.dump({"results": results}, open(f, "w"))
+    rows = analysis.load([f])
+    t_delay, t_loss = analysis.table(rows, network=True), analysis.table(rows, network=True, rule="loss")
+    assert "| distributed | 25.0 | 0.0250 |" in t_delay and "loss" not in t_delay     # max over ranks (Q16)
+    assert "| trainer | loss % |" in t_loss and "| distributed | 0.5 | 0.0300 |" in t_loss
+    out = analysis.plot(rows, tmp_path / "loss.png", network=True, rule="loss")
+    assert Path(out).exists()
+
+
+def test_deploy_assets_and_launcher_auto(tmp_path):
+    """O4-O6 analogues: the compose file parses and describes one all-GPU trainer plus the two-container rendezvous;
+    the image bakes no SSH key; `launch -n auto` resolves to one rank per visible GPU (one rank on a CPU machine)."""
+    import yaml
+    compose = yaml.safe_load(open(ROOT / "deploy" / "docker-compose.yaml"))
+    assert set(compose["services"]) == {"trainer", "master", "worker"}
+    assert compose["services"]["trainer"]["ipc"] == "host"                    # symmetric memory across the ranks of a node
+    for svc in ("master", "worker"):
+        assert "B200RNN_COMM=nccl" in compose["services"][svc]["environment"] and "--nnodes 2" in compose["services"][svc]["command"]
+    docker = "\n".join(ln for ln in (ROOT / "deploy" / "Dockerfile").read_text().splitlines() if not ln.lstrip().startswith("#"))
+    assert "pytorch_distributed_rnn_b200._build" in docker and "id_rsa" not in docker and "ssh" not in docker
+    script = tmp_path / "who.py"
+    script.write_text("import os; print('rank', os.environ['RANK'], 'of', os.environ['WORLD_SIZE'])")
+    cp = subprocess.run([sys.executable, "-m", "pytorch_distributed_rnn_b200.parallel.launch", "-n", "auto", str(script)],
+                        capture_output=True, text=True, cwd=ROOT, env={**__import__("os").environ, "CUDA_VISIBLE_DEVICES": ""})
+    assert cp.returncode == 0 and cp.stdout.strip() == "rank 0 of 1", cp.stderr

@@ -80,6 +80,36 @@ def test_world1_allreduce_broadcast_barrier(comm1):
 
 
 @pytest.mark.gpu
+def test_injected_loss_costs_retransmission_timeouts_and_keeps_results(comm1):
+    """`tc netem loss` analogue: at 100 % every publication pays the full run of 8 retransmission timeouts, at 0 %
+    none; the values that arrive are the same either way."""
+    a = torch.randn(14150, device="cuda")
+    want = a.clone()
+
+    def timed(algo):
+        v = a.clone()
+        comm1.allreduce_flat(v, average=False, algo=algo)       # warm
+        v.copy_(a)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        comm1.allreduce_flat(v, average=False, algo=algo)
+        e1.record()
+        torch.cuda.synchronize()
+        assert torch.equal(v, want)
+        return e0.elapsed_time(e1) * 1e3                        # us
+
+    for algo in (4, 1):
+        base = timed(algo)
+        comm1.set_loss(100.0, rto_ns=50_000)
+        lossy = timed(algo)
+        comm1.set_loss(0.0)
+        assert lossy > base + 0.5 * 8 * 50 and lossy < base + 4 * 8 * 50 + 200, (algo, base, lossy)
+    with pytest.raises(ValueError):
+        comm1.set_loss(101.0)
+    comm1.check()
+
+
+@pytest.mark.gpu
 @pytest.mark.multigpu
 def test_watchdog_trips_instead_of_hanging():
     """A rank that never joins an all-reduce: the others' in-kernel waits time out (B200RNN_COMM_TIMEOUT_MS),

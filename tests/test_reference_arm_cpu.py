@@ -52,7 +52,7 @@ def test_network_sweep_splits_one_log_into_per_delay_entries(tmp_path, monkeypat
     monkeypatch.setattr(sweep.subprocess, "run", lambda *a, **k: CP())
 
     class A:
-        dataset_path, results, delays = tmp_path / "ds", str(tmp_path / "net.json"), "0,50,400"
+        dataset_path, results, delays, losses = tmp_path / "ds", str(tmp_path / "net.json"), "0,50,400", ""
     sweep.run_network(A(), 2)
     res = json.load(open(A.results))["results"]
     assert len(res) == 6                                  # 3 delays x 2 trainers
