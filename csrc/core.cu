@@ -255,16 +255,26 @@ extern "C" int b200rnn_fused_update(const float* rows, int32_t n_rows, int64_t n
   return B200RNN_OK;
 }
 
+namespace {
+constexpr int kHeadFwdThreads = 128, kHeadFwdMaxGrid = 64;
+inline int head_fwd_grid(int32_t batch) {
+  const int warps = kHeadFwdThreads / 32;
+  const int grid = (batch + warps - 1) / warps;
+  return grid > kHeadFwdMaxGrid ? kHeadFwdMaxGrid : (grid < 1 ? 1 : grid);
+}
+}  // namespace
+
+extern "C" int64_t b200rnn_head_fwd_metrics_floats(int32_t batch) { return 2 * ((int64_t)head_fwd_grid(batch) + 1); }
+
 extern "C" int b200rnn_head_fwd(const float* h_last, int64_t ld_h, const float* fc_w, const float* fc_b,
                                 const int64_t* labels, int32_t batch, int32_t hidden, int32_t classes,
                                 float* logits, float* metrics, void* stream) {
   B200_REQUIRE(h_last && fc_w && fc_b && batch >= 1 && hidden >= 1 && classes >= 1, B200RNN_EINVAL,
                "head_fwd: bad argument");
   B200_REQUIRE(classes <= 1024, B200RNN_ETOOBIG, "head_fwd: classes=%d exceeds 1024", classes);
-  // metrics doubles as the partial buffer: needs 2 * (grid + 1) floats when labels are given.
-  const int threads = 128, warps = threads / 32;
-  int grid = (batch + warps - 1) / warps;
-  if (grid > 64) grid = 64;
+  // metrics doubles as the partial buffer: b200rnn_head_fwd_metrics_floats(batch) floats when labels are given.
+  const int threads = kHeadFwdThreads, warps = threads / 32;
+  const int grid = head_fwd_grid(batch);
   float* part = (labels && metrics) ? metrics + 2 : nullptr;
   head_fwd_kernel<<<grid, threads, warps * classes * sizeof(float), (cudaStream_t)stream>>>(
       h_last, ld_h, fc_w, fc_b, labels, batch, hidden, classes, logits, part);

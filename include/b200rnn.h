@@ -210,7 +210,10 @@ int b200rnn_reduce_rows(const float* rows, int32_t n_rows, int64_t row_floats,
 
 /* ---- K5: classifier head, standalone form (evaluation and autograd path).
  * h_last [B,H] (row stride ld_h floats), logits out [B,C] (nullable),
- * metrics out: [0] = sum of per-sample CE losses, [1] = correct count. */
+ * metrics out: [0] = sum of per-sample CE losses, [1] = correct count.  When labels are given, `metrics` also
+ * carries the per-block partial sums behind those two values (combined in fixed order by a second launch): it
+ * must then hold b200rnn_head_fwd_metrics_floats(batch) floats (at most 130), not 2. */
+int64_t b200rnn_head_fwd_metrics_floats(int32_t batch);
 int b200rnn_head_fwd(const float* h_last, int64_t ld_h, const float* fc_w, const float* fc_b,
                      const int64_t* labels, int32_t batch, int32_t hidden, int32_t classes,
                      float* logits, float* metrics, void* stream);

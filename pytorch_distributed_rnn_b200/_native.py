@@ -103,6 +103,7 @@ def _declare(lib: C.CDLL) -> None:
         "b200rnn_gru_bwd_dx": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
         "b200rnn_lstm_bwd_static": (i32, [P(ModelDesc), vp, vp, vp, vp, f32, vp, vp, vp, vp, vp]),
         "b200rnn_reduce_rows": (i32, [vp, i32, i64, vp, i32, vp]),
+        "b200rnn_head_fwd_metrics_floats": (i64, [i32]),
         "b200rnn_head_fwd": (i32, [vp, i64, vp, vp, vp, i32, i32, i32, vp, vp, vp]),
         "b200rnn_fused_update": (i32, [vp, i32, i64, vp, vp, vp, P(OptimDesc), vp, vp, vp]),
         "b200rnn_l2_flush": (i32, [vp, i64, vp]),
