@@ -617,16 +617,18 @@ __global__ void __launch_bounds__(kThreads) ps_push_kernel(
   for (int r = 0; r < n_rows; ++r) g += rows[(long long)r * row_stride + i];
   if (i >= n) { if (metrics != nullptr) metrics[i - n] = g; return; }
   g *= o.grad_scale;
-  float p = 0.0f;                       // apply_update on p = 0 yields the DELTA of this step
+  float* sp = reinterpret_cast<float*>(c.base[server] + c.off_heap + heap_off) + i;
+  // The DELTA of this step goes to the server: apply_update on p = 0 yields it directly; with weight decay the
+  // update depends on the parameter itself, so the server's current value is read over NVLink first (another
+  // worker may change it before the add lands: asynchronous by design, like the reference's parameter server).
+  const float p0 = (o.wd != 0.0f) ? *reinterpret_cast<const volatile float*>(sp) : 0.0f;
+  float p = p0;
   float m = exp_avg ? exp_avg[i] : 0.0f;
   float v = exp_avg_sq ? exp_avg_sq[i] : 0.0f;
-  OptScalars od = o;
-  od.wd = 0.0f;                         // weight decay would need the remote value; not supported here
-  apply_update(od, g, p, m, v);
+  apply_update(o, g, p, m, v);
   if (exp_avg) exp_avg[i] = m;
   if (exp_avg_sq) exp_avg_sq[i] = v;
-  float* sp = reinterpret_cast<float*>(c.base[server] + c.off_heap + heap_off) + i;
-  atomicAdd(sp, p);                     // RED.ADD.F32 to peer memory
+  atomicAdd(sp, p - p0);                // RED.ADD.F32 to peer memory
 }
 __global__ void __launch_bounds__(kThreads) ps_pull_kernel(Ctx c, int server, long long heap_off, float* __restrict__ dst, long long n) {
   const volatile float* sp = reinterpret_cast<const volatile float*>(c.base[server] + c.off_heap + heap_off);

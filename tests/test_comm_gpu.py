@@ -80,6 +80,34 @@ def test_world1_allreduce_broadcast_barrier(comm1):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("wd", [0.0, 0.05])
+def test_world1_ps_push_matches_torch_adam_with_weight_decay(comm1, wd):
+    """K10 on one GPU (server == worker): three pushes equal three torch Adam steps, weight decay included (the delta
+    then depends on the server's current value, which the kernel reads before it adds)."""
+    torch.manual_seed(1)
+    lin = torch.nn.Linear(37, 11).cuda()
+    ref = copy.deepcopy(lin)
+    arena = comm1.make_arena(lin)
+    opt = FusedAdam(arena, lr=0.01, weight_decay=wd)
+    ropt = torch.optim.Adam(ref.parameters(), lr=0.01, weight_decay=wd)
+    P = arena.numel
+    for step in range(3):
+        rows = torch.randn(4, P + 2, device="cuda")
+        opt.step_count += 1
+        slot = torch.zeros(2, device="cuda")
+        comm1.ps_push(rows, 4, P, opt, opt.desc(grad_scale=1.0), slot, 0, arena.heap_off)
+        g = rows[:, :P].sum(0)
+        off = 0
+        for p in ref.parameters():
+            p.grad = g[off:off + p.numel()].view_as(p).clone()
+            off += p.numel()
+        ropt.step()
+        assert torch.allclose(slot, rows[:, P:].sum(0), rtol=1e-5)
+    comm1.check()
+    assert torch.allclose(arena.flat[:P], torch.cat([p.detach().view(-1) for p in ref.parameters()]), atol=2e-6)
+
+
+@pytest.mark.gpu
 def test_injected_loss_costs_retransmission_timeouts_and_keeps_results(comm1):
     """`tc netem loss` analogue: at 100 % every publication pays the full run of 8 retransmission timeouts, at 0 %
     none; the values that arrive are the same either way."""
