@@ -165,10 +165,11 @@ def split_network_log(log):
     """{(rule_type, value string): log text} from a `--delay-sweep-us` / `--loss-sweep-pct` job's stderr: every rank's
     log contributes one segment per rule, behind its `Injected delay: N us` / `Injected loss: P %` marker."""
     import re
-    parts = re.split(r"^.*Injected (delay|loss): ([0-9.]+) (?:us|%).*$", log, flags=re.M)
+    parts = re.split(r"^.*Injected (delay|loss|warmup): ([0-9.]+) (?:us|%).*$", log, flags=re.M)
     by_rule = {}
     for kind, value, text in zip(parts[1::3], parts[2::3], parts[3::3]):
-        by_rule[(kind, value)] = by_rule.get((kind, value), "") + text
+        if kind != "warmup":      # the sweep's untimed first run
+            by_rule[(kind, value)] = by_rule.get((kind, value), "") + text
     return by_rule
 
 

@@ -60,12 +60,13 @@ def _write_history(args, train_history, validation_history) -> None:
 
 DELAY_MARK = "Injected delay: {} us"      # bench/sweep.py splits a sweep's log at these lines
 LOSS_MARK = "Injected loss: {} %"
+WARMUP_MARK = "Injected warmup: 0 us"     # the untimed first run of a sweep
 
 
 def _network_sweep(args, trainer, delays_us=(), losses_pct=()):
     """The reference's network experiment (tc netem delay / loss on every host, one job per rule:
     fabfile.py:130-191) as ONE job: after an untimed warm-up run (first-use costs: module load, buffer
-    allocation), the same ``--epochs`` training is repeated once per injected rule; every repetition logs the
+    allocation, behind an ``Injected warmup`` marker), the same ``--epochs`` training is repeated once per injected rule; every repetition logs the
     usual performance line behind a ``Injected delay: N us`` / ``Injected loss: P %`` marker.  A delay is spun
     on the device in front of every flag publication of the in-kernel collectives (`SymmComm.set_delay_ns`),
     i.e. it lengthens every message's latency; a loss makes that publication pay a retransmission timeout with
@@ -74,10 +75,10 @@ def _network_sweep(args, trainer, delays_us=(), losses_pct=()):
     if comm is None or not hasattr(comm, "set_delay_ns"):
         raise SystemExit("--delay-sweep-us / --loss-sweep-pct need the in-kernel NVLink communicator "
                          "(a multi-GPU distributed / horovod run)")
-    level = logging.getLogger().level
-    logging.getLogger().setLevel(logging.WARNING)
-    trainer.train(epochs=args.epochs)                       # warm-up, not reported
-    logging.getLogger().setLevel(level)
+    # warm-up at the normal log level (the first INFO-level epoch pays one-off costs of its own: ~3 ms on B200, as much
+    # as a whole epoch); bench/sweep.py drops the segment behind this marker
+    logging.info(WARMUP_MARK)
+    trainer.train(epochs=args.epochs)
     rules = [(DELAY_MARK, d, lambda v: comm.set_delay_ns(v * 1000)) for d in delays_us]
     rules += [(LOSS_MARK, p, lambda v: comm.set_loss(v)) for p in losses_pct]
     for mark, value, apply in rules:

@@ -60,6 +60,7 @@ def test_network_log_split_and_loss_rule_tables(tmp_path):
     import analysis
     import sweep
     log = ("INFO:root:Training set of size 6912\n"
+           "INFO:root:Injected warmup: 0 us\nINFO:root:0: Memory Usage: 900.0, Training Duration: 9.000\n"
            "INFO:root:Injected delay: 0 us\nINFO:root:0: Memory Usage: 900.0, Training Duration: 0.010\n"
            "INFO:root:Injected delay: 25 us\nINFO:root:0: Memory Usage: 900.0, Training Duration: 0.020\n"
            "INFO:root:Injected loss: 0.5 %\nINFO:root:0: Memory Usage: 900.0, Training Duration: 0.030\n"
