@@ -54,3 +54,47 @@ def test_gru_cell_trains_and_checkpoints_load_into_stock_gru(tiny_dataset_dir, t
         want = gru(x)[0][:, -1] @ state["fc.weight"].t() + state["fc.bias"]
         got = t.model(x)
     assert torch.allclose(got, want, atol=1e-5)
+
+
+def test_network_sweep_sequences_rules_and_resets_the_communicator(caplog):
+    """`--delay-sweep-us` / `--loss-sweep-pct` (fabfile.py:146-191 in one job): a marked warm-up run, then one run per
+    rule with exactly that rule active, and a clean communicator afterwards."""
+    import logging
+    import types
+    from pytorch_distributed_rnn_b200 import trainer as tr
+
+    class Comm:
+        def __init__(self):
+            self.delay, self.loss, self.log = 0, 0.0, []
+
+        def set_delay_ns(self, ns):
+            self.delay = ns
+
+        def set_loss(self, pct, rto_ns=0):
+            self.loss = pct
+
+    class T:
+        start_epoch = 7
+
+        def __init__(self):
+            self.comm, self.runs = Comm(), []
+
+        def _get_comm(self):
+            return self.comm
+
+        def train(self, epochs):
+            self.runs.append((self.comm.delay, self.comm.loss, self.start_epoch))
+
+    t = T()
+    with caplog.at_level(logging.INFO):
+        tr._network_sweep(types.SimpleNamespace(epochs=1), t, delays_us=[0, 50], losses_pct=[0.5, 15])
+    assert t.runs == [(0, 0.0, 7), (0, 0.0, 0), (50000, 0.0, 0), (0, 0.5, 0), (0, 15, 0)]
+    assert (t.comm.delay, t.comm.loss) == (0, 0.0)
+    marks = [r.getMessage() for r in caplog.records if r.getMessage().startswith("Injected")]
+    assert marks == ["Injected warmup: 0 us", "Injected delay: 0 us", "Injected delay: 50 us", "Injected loss: 0.5 %", "Injected loss: 15 %"]
+
+    class NoComm(T):
+        def _get_comm(self):
+            return None
+    with pytest.raises(SystemExit):
+        tr._network_sweep(types.SimpleNamespace(epochs=1), NoComm(), delays_us=[1])
