@@ -469,7 +469,7 @@ int b200rnn_comm_broadcast(const b200rnn_comm_ctx* ctx, uint32_t seq, int64_t he
 int b200rnn_comm_put(const b200rnn_comm_ctx* ctx, uint32_t seq, int32_t dst, const void* src,
                      int64_t heap_off, int64_t bytes, void* stream);
 int b200rnn_comm_wait(const b200rnn_comm_ctx* ctx, uint32_t seq, int32_t src, void* stream);
-/* K10: one-sided parameter server (src/motion/param_server/*).  The server rank hosts the shared
+/* K10: one-sided parameter server (the src/motion/param_server package).  The server rank hosts the shared
  * parameters at heap offset heap_off of ITS symmetric heap and does nothing else.  ps_pull copies them
  * into dst with peer loads; ps_push reduces the worker's gradient rows, runs the worker's OWN
  * optimizer state (exp_avg / exp_avg_sq live on the worker) and adds the resulting parameter delta to
