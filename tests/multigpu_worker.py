@@ -172,7 +172,7 @@ def main():
         tl = torch.nn.functional.cross_entropy(twin(xb), yb)
         tl.backward()
         topt.step()
-        lay &= abs(float(mine[0]) / 16 - float(tl)) < 2e-2 * max(1.0, abs(float(tl)))
+        lay &= abs(float(mine[0]) / 16 - float(tl.detach())) < 2e-2 * max(1.0, abs(float(tl.detach())))
     torch.cuda.synchronize()
     pd = torch.cat([(p.detach() - q.detach()).abs().view(-1) for p, q in zip(big.parameters(), twin.module.parameters())])
     res["layered_param_mean_abs_diff"] = float(pd.mean())
