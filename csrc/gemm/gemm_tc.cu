@@ -107,7 +107,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     if (!ok && lane == 0) atomicExch(&g_gemm_error, 3);
     tc_fence_after_sync();
     const int q = warp & 3;
-    const int row = m0 + q * 32 + lane;
     float* Cf = reinterpret_cast<float*>(Cout);
     __nv_bfloat16* Cb = reinterpret_cast<__nv_bfloat16*>(Cout);
     // TMEM gives each lane one output ROW; writing it out directly would scatter every store instruction

@@ -32,7 +32,6 @@ constexpr int H = 32;
 constexpr int NT = 128;          // threads = gate rows = TMEM lanes
 constexpr int NS = 16;           // sample columns of the MMA (N)
 constexpr int KMAX = 64;         // max operand width (stacked layers: H + H)
-constexpr int A_BYTES = 128 * KMAX * 4;   // 32 KiB per split part
 constexpr int B_BYTES = NS * KMAX * 4;    // 4 KiB per split part per buffer
 constexpr int TC_SMEM = 4 * B_BYTES + 64 + 128;
 
