@@ -123,7 +123,7 @@ int b200rnn_lstm_bwd(const b200rnn_model_desc* d, const float* params,
                      float loss_scale, const float* d_out, const float* d_hn,
                      const float* d_cn, float* scratch, void* stream);
 
-/* GRU members of the same fused family (hidden_size == 32, d->cell == B200RNN_CELL_GRU;
+/* GRU members of the same fused family (hidden_size 32 or 16, d->cell == B200RNN_CELL_GRU;
  * torch gate order r, z, n; SURVEY P22 — the reference itself only builds nn.LSTM).  Same
  * tiling, stash layout (h_seq | unused | per-step (r, z, n, W_hn h + b_hn)), scratch layout and
  * fused head + cross-entropy as the LSTM entry points; a GRU has no cell state, so no d_cn. */
