@@ -57,17 +57,19 @@ def table(rows, network=False, rule="delay"):
     for r in rows:
         groups[key(r)].append(r)
     out = []
-    head = f"| trainer | {'loss %' if rule == 'loss' else 'delay us'} | s | samples/s | n |" if network else "| trainer | ranks | batch | s | samples/s | MiB | n |"
+    head = (f"| trainer | {'loss %' if rule == 'loss' else 'delay us'} | s | samples/s | n | sd s |" if network
+            else "| trainer | ranks | batch | s | samples/s | MiB | n | sd s |")
     out.append(head)
     out.append("|" + "---|" * (head.count("|") - 1))
     for k in sorted(groups, key=lambda x: tuple(str(v) if v is None else v for v in x)):
         g = groups[k]
         s = statistics.mean(x["seconds"] for x in g)
         sps = g[0]["samples"] / s
+        sd = f"{statistics.stdev(x['seconds'] for x in g):.4f}" if len(g) > 1 else "-"   # the notebooks draw a 68 % band
         if network:
-            out.append(f"| {k[0]} | {k[1]} | {s:.4f} | {sps:.0f} | {len(g)} |")
+            out.append(f"| {k[0]} | {k[1]} | {s:.4f} | {sps:.0f} | {len(g)} | {sd} |")
         else:
-            out.append(f"| {k[0]} | {k[1]} | {k[2]} | {s:.4f} | {sps:.0f} | {statistics.mean(x['memory'] for x in g):.0f} | {len(g)} |")
+            out.append(f"| {k[0]} | {k[1]} | {k[2]} | {s:.4f} | {sps:.0f} | {statistics.mean(x['memory'] for x in g):.0f} | {len(g)} | {sd} |")
     return "\n".join(out)
 
 
@@ -81,7 +83,8 @@ def _series(rows, network):
                 pts[r[xs]].append(r["seconds"])
         if pts:
             k = sorted(pts)
-            out[tr] = (k, [statistics.mean(pts[x]) for x in k])
+            out[tr] = (k, [statistics.mean(pts[x]) for x in k],
+                       [statistics.stdev(pts[x]) if len(pts[x]) > 1 else 0.0 for x in k])
     return out
 
 
@@ -99,8 +102,8 @@ def plot(rows, path, network=False, rule="delay"):
     except ImportError:
         return _plot_svg(series, Path(path).with_suffix(".svg"), xlabel)
     fig, ax = plt.subplots(figsize=(6, 4))
-    for tr, (k, v) in series.items():
-        ax.plot(k, v, marker="o", label=tr)
+    for tr, (k, v, sd) in series.items():
+        ax.errorbar(k, v, yerr=sd if any(sd) else None, marker="o", capsize=3, label=tr)   # +-1 sd = the notebooks' 68 % band
     ax.set_xlabel(xlabel)
     ax.set_ylabel("Training Time (s)")
     ax.legend()
@@ -111,8 +114,8 @@ def plot(rows, path, network=False, rule="delay"):
 
 def _plot_svg(series, path, xlabel, w=640, h=420):
     ml, mr, mt, mb = 70, 20, 20, 50
-    xs = sorted({x for k, _ in series.values() for x in k})
-    ys = [y for _, v in series.values() for y in v]
+    xs = sorted({x for k, _, _ in series.values() for x in k})
+    ys = [y + e for _, v, sd in series.values() for y, e in zip(v, sd)]
     if not xs or not ys:
         return None
     x0, x1, y1 = min(xs), max(xs), max(ys) * 1.08
@@ -131,12 +134,14 @@ def _plot_svg(series, path, xlabel, w=640, h=420):
         o.append(f'<line x1="{ml}" y1="{sy(y):.1f}" x2="{w - mr}" y2="{sy(y):.1f}" stroke="#dddddd"/>')
     o.append(f'<text x="{(ml + w - mr) / 2}" y="{h - 10}" text-anchor="middle">{xlabel}</text>')
     o.append(f'<text x="16" y="{(mt + h - mb) / 2}" text-anchor="middle" transform="rotate(-90 16 {(mt + h - mb) / 2})">Training Time (s)</text>')
-    for i, (tr, (k, v)) in enumerate(series.items()):
+    for i, (tr, (k, v, sd)) in enumerate(series.items()):
         c = colors[i % len(colors)]
         pts = " ".join(f"{sx(x):.1f},{sy(y):.1f}" for x, y in zip(k, v))
         o.append(f'<polyline points="{pts}" fill="none" stroke="{c}" stroke-width="2"/>')
-        for x, y in zip(k, v):
+        for x, y, e in zip(k, v, sd):
             o.append(f'<circle cx="{sx(x):.1f}" cy="{sy(y):.1f}" r="3.5" fill="{c}"/>')
+            if e > 0:   # +-1 standard deviation over the repeats
+                o.append(f'<line x1="{sx(x):.1f}" y1="{sy(y - e):.1f}" x2="{sx(x):.1f}" y2="{sy(y + e):.1f}" stroke="{c}"/>')
         o.append(f'<rect x="{w - mr - 130}" y="{mt + 18 * i}" width="12" height="12" fill="{c}"/>')
         o.append(f'<text x="{w - mr - 112}" y="{mt + 18 * i + 11}">{tr}</text>')
     o.append("</svg>")
