@@ -1,4 +1,6 @@
-"""Shared pieces of the toy plumbing examples (E1-E4): the 24-sample regression task and one pass over it.
+"""Shared pieces of the toy plumbing examples (E1-E4): the 24-sample regression task and one pass over it
+(the reference repeats them in each script: src/example/example_ddp.py:11-32,40-92, example_horovod.py,
+example_single.py).
 
 Each example only differs in HOW gradients are synchronised (not at all / DDP wrapper / Horovod-style optimizer);
 the optimisation pass and the lines it prints (``parameters:`` is what the tests compare across ranks) live here.

@@ -2,7 +2,8 @@
 
 A ``[M,K]`` and B ``[N,K]`` are bf16, row-major; C is fp32 or bf16.  This is the K1/K4 building
 block: input projection over all timesteps, per-step recurrent projection at large hidden sizes
-and weight-gradient GEMMs (see include/b200rnn.h).  Library GEMMs (cuBLAS via torch.matmul)
+and weight-gradient GEMMs (see include/b200rnn.h) — the products ATen / MKL compute inside
+``nn.LSTM`` and its autograd backward for the reference (src/motion/model.py:9-14, trainer/base.py:116).  Library GEMMs (cuBLAS via torch.matmul)
 are used nowhere on these paths.
 """
 from __future__ import annotations

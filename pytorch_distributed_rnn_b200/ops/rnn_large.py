@@ -1,4 +1,5 @@
-"""Autograd glue for the large-hidden LSTM / GRU path (csrc/rnn/rnn_large.cu).
+"""Autograd glue for the large-hidden LSTM / GRU path (csrc/rnn/rnn_large.cu): what ``nn.LSTM(..., batch_first=True)``
+does for the reference model when ``--hidden-units`` is large (src/motion/model.py:9-14, main.py:21).
 
 Covers every shape with ``hidden % 8 == 0`` that the small fused family does not (in particular the
 scaled configuration of BASELINE.json: 2 layers, hidden 1024, seq_len 512, bf16): the input
