@@ -3,7 +3,9 @@
 API surface the reference uses from ``horovod.torch`` (src/motion/trainer/horovod.py:17-42,
 src/example/example_horovod.py:42-53,80-83): ``init``, ``rank``, ``size``, ``local_rank``,
 ``broadcast_parameters(state_dict, root_rank)``, ``DistributedOptimizer(optimizer,
-named_parameters)``, plus ``allreduce`` / ``broadcast_optimizer_state`` for completeness.
+named_parameters)``, plus the rest of the everyday ``horovod.torch`` vocabulary so that other scripts written
+against it keep working: ``allreduce`` / ``allreduce_`` (``op=Average | Sum``), ``broadcast`` / ``broadcast_``,
+``allgather``, ``broadcast_optimizer_state``, ``local_size``, ``is_initialized``, ``barrier`` / ``join``, ``shutdown``.
 
 Horovod's C++ core negotiates tensor readiness by name through a rank-0 coordinator and
 packs ready tensors into a fusion buffer each cycle.  Training graphs here are static, so
@@ -52,10 +54,87 @@ def local_rank() -> int:
     return pg.rank_info().local_rank
 
 
-def allreduce(tensor: torch.Tensor, average: bool = True) -> torch.Tensor:
-    out = tensor.clone()
-    _c().allreduce_flat(out.view(-1), average=average)
-    return out
+def local_size() -> int:
+    """Ranks on this node (one per GPU): what the launcher / torchrun export as LOCAL_WORLD_SIZE, else the world."""
+    import os
+    return int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("OMPI_COMM_WORLD_LOCAL_SIZE", size())))
+
+
+def is_initialized() -> bool:
+    return _comm is not None
+
+
+def shutdown() -> None:
+    """Release the communicator (symmetric memory, peer mappings) and the process group."""
+    global _comm
+    if _comm is not None and hasattr(_comm, "close"):
+        _comm.close()
+    _comm = None
+    pg.shutdown()
+
+
+Average, Sum = "average", "sum"     # reduction ops of allreduce (horovod.torch.Average / Sum)
+
+
+def _want_average(average, op) -> bool:
+    if op is not None:
+        if op not in (Average, Sum):
+            raise ValueError(f"unsupported reduction op {op!r} (Average or Sum)")
+        if average is not None:
+            raise ValueError("pass either average= or op=, not both")
+        return op == Average
+    return True if average is None else bool(average)
+
+
+def allreduce_(tensor: torch.Tensor, average: Optional[bool] = None, op: Optional[str] = None) -> torch.Tensor:
+    """In-place all-reduce of a contiguous tensor (default: average)."""
+    if not tensor.is_contiguous():
+        raise ValueError("allreduce_: tensor must be contiguous")
+    _c().allreduce_flat(tensor.detach().view(-1), average=_want_average(average, op))
+    return tensor
+
+
+def allreduce(tensor: torch.Tensor, average: Optional[bool] = None, op: Optional[str] = None) -> torch.Tensor:
+    return allreduce_(tensor.detach().clone().contiguous(), average=average, op=op)
+
+
+def broadcast_(tensor: torch.Tensor, root_rank: int = 0) -> torch.Tensor:
+    if size() > 1:
+        flat = tensor.detach().contiguous().view(-1)
+        _c().broadcast_flat(flat, root=root_rank)
+        if flat.data_ptr() != tensor.data_ptr():
+            tensor.detach().copy_(flat.view_as(tensor))
+    return tensor
+
+
+def broadcast(tensor: torch.Tensor, root_rank: int = 0) -> torch.Tensor:
+    return broadcast_(tensor.detach().clone(), root_rank)
+
+
+def allgather(tensor: torch.Tensor) -> torch.Tensor:
+    """Concatenation of every rank's tensor along dimension 0 (first dimensions may differ, as in Horovod).  A
+    convenience outside the training step: it goes through the process group's all_gather."""
+    if size() == 1:
+        return tensor.detach().clone()
+    t = tensor.detach().contiguous()
+    n = torch.tensor([t.shape[0] if t.dim() else 1], dtype=torch.int64, device=t.device)
+    counts = [torch.zeros_like(n) for _ in range(size())]
+    dist.all_gather(counts, n)
+    counts = [int(c) for c in counts]
+    rows = t.reshape(counts[rank()], -1) if t.dim() else t.reshape(1, 1)
+    pad = torch.zeros(max(counts), rows.shape[1], dtype=t.dtype, device=t.device)
+    pad[:rows.shape[0]] = rows
+    parts = [torch.empty_like(pad) for _ in range(size())]
+    dist.all_gather(parts, pad)
+    out = torch.cat([p[:c] for p, c in zip(parts, counts)], 0)
+    return out.reshape(sum(counts), *t.shape[1:]) if t.dim() else out.reshape(-1)
+
+
+def barrier() -> None:
+    _c().barrier()
+
+
+join = barrier   # horovod.torch.join(): wait for every rank (there is no uneven-data handling to flush here)
 
 
 def broadcast_parameters(params, root_rank: int = 0) -> None:

@@ -114,3 +114,11 @@ def test_parameter_server_cpu(tiny_dataset_dir, tmp_path):
     assert "RPC shutdown on parameter server. (4 asynchronous updates applied)" in outs[0][0]  # 2 workers x 64/32 batches
     for r in (1, 2):
         assert len(STEP_RE.findall(outs[r][1])) == 2 and f"{r}: Memory Usage:" in outs[r][1]
+
+
+def test_horovod_style_api_surface():
+    """The everyday horovod.torch vocabulary beyond what the reference's trainer touches (allreduce ops, in-place
+    forms, broadcast, uneven allgather, join, shutdown) on gloo, world size 2."""
+    res = launch([PY, str(ROOT / "tests" / "hvd_api_worker.py")], 2, timeout=240, env={"OMP_NUM_THREADS": "1"})
+    _ok(res)
+    assert all("hvd api ok" in cp.stdout for cp in res)
