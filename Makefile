@@ -2,7 +2,7 @@
 PY ?= python
 NPROC ?= auto
 
-.PHONY: build rebuild test test-gpu test-multigpu smoke bench bench-reference bench-scaled wheel sass clean
+.PHONY: build rebuild test test-gpu test-multigpu smoke bench bench-reference bench-scaled train wheel sass clean
 
 build:            ## compile csrc/ for sm_100a into pytorch_distributed_rnn_b200/_lib/libb200rnn.so (only if stale)
 	$(PY) -m pytorch_distributed_rnn_b200._build
