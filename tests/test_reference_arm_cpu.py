@@ -66,3 +66,20 @@ def test_network_sweep_splits_one_log_into_per_delay_entries(tmp_path, monkeypat
     assert abs(got[("distributed", 400.0)] - 0.0041) < 1e-9   # max over ranks
     sweep.run_network(A(), 2)                             # resume: nothing is run or recorded twice
     assert len(json.load(open(A.results))["results"]) == 6
+
+
+def test_bench_prints_exactly_one_json_line_without_a_gpu():
+    """bench.py's stdout contract (one JSON line, exit 0) also holds where it cannot measure: without a CUDA device both
+    arms say so instead of crashing or printing library chatter."""
+    import subprocess
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is visible: covered by the real bench runs")
+    for extra in ([], ["--impl", "reference"], ["--config", "scaled"]):
+        cp = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--steps", "1", "--warmup", "3", *extra],
+                            capture_output=True, text=True, timeout=300, cwd=ROOT)
+        assert cp.returncode == 0, cp.stderr[-2000:]
+        lines = [l for l in cp.stdout.splitlines() if l.strip()]
+        assert len(lines) == 1, cp.stdout
+        d = json.loads(lines[0])
+        assert d["impl"] == ("reference" if "reference" in extra else "own") and "CUDA" in d["unavailable"]
