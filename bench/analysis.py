@@ -73,14 +73,14 @@ def table(rows, network=False, rule="delay"):
     return "\n".join(out)
 
 
-def _series(rows, network):
+def _series(rows, network, metric="seconds"):
     xs = "rule_value" if network else "ranks"
     out = {}
     for tr in sorted({r["trainer"] for r in rows}):
         pts = defaultdict(list)
         for r in rows:
             if r["trainer"] == tr and r[xs] is not None:
-                pts[r[xs]].append(r["seconds"])
+                pts[r[xs]].append(r[metric])
         if pts:
             k = sorted(pts)
             out[tr] = (k, [statistics.mean(pts[x]) for x in k],
@@ -88,31 +88,36 @@ def _series(rows, network):
     return out
 
 
-def plot(rows, path, network=False, rule="delay"):
-    """Training time vs ranks (or injected delay) per trainer.  matplotlib (Agg) when it is installed, else a
+def plot(rows, path, network=False, rule="delay", metric="seconds"):
+    """Training time (or peak memory, ``metric="memory"``) vs ranks (or injected delay / loss) per trainer, the `local`
+    trainer as a dashed horizontal baseline like in Experiments.ipynb.  matplotlib (Agg) when it is installed, else a
     dependency-free SVG with the same content (``path`` then gets the .svg suffix); returns the file written."""
     if network:
         rows = [r for r in rows if (r.get("rule_type") or "delay") == rule]
-    series = _series(rows, network)
+    series = _series(rows, network, metric)
+    ylabel = "Memory (MiB)" if metric == "memory" else "Training Time (s)"
     xlabel = ("injected loss (%)" if rule == "loss" else "injected delay (us)") if network else "ranks (GPUs)"
     try:
         import matplotlib
         matplotlib.use("Agg")
         import matplotlib.pyplot as plt
     except ImportError:
-        return _plot_svg(series, Path(path).with_suffix(".svg"), xlabel)
+        return _plot_svg(series, Path(path).with_suffix(".svg"), xlabel, ylabel)
     fig, ax = plt.subplots(figsize=(6, 4))
     for tr, (k, v, sd) in series.items():
+        if len(k) == 1 and len(series) > 1:      # the single-rank baseline
+            ax.axhline(v[0], linestyle="--", color="gray", label=tr)
+            continue
         ax.errorbar(k, v, yerr=sd if any(sd) else None, marker="o", capsize=3, label=tr)   # +-1 sd = the notebooks' 68 % band
     ax.set_xlabel(xlabel)
-    ax.set_ylabel("Training Time (s)")
+    ax.set_ylabel(ylabel)
     ax.legend()
     fig.tight_layout()
     fig.savefig(path, dpi=120)
     return path
 
 
-def _plot_svg(series, path, xlabel, w=640, h=420):
+def _plot_svg(series, path, xlabel, ylabel="Training Time (s)", w=640, h=420):
     ml, mr, mt, mb = 70, 20, 20, 50
     xs = sorted({x for k, _, _ in series.values() for x in k})
     ys = [y + e for _, v, sd in series.values() for y, e in zip(v, sd)]
@@ -133,10 +138,12 @@ def _plot_svg(series, path, xlabel, w=640, h=420):
         o.append(f'<text x="{ml - 6}" y="{sy(y) + 4:.1f}" text-anchor="end">{y:.4g}</text>')
         o.append(f'<line x1="{ml}" y1="{sy(y):.1f}" x2="{w - mr}" y2="{sy(y):.1f}" stroke="#dddddd"/>')
     o.append(f'<text x="{(ml + w - mr) / 2}" y="{h - 10}" text-anchor="middle">{xlabel}</text>')
-    o.append(f'<text x="16" y="{(mt + h - mb) / 2}" text-anchor="middle" transform="rotate(-90 16 {(mt + h - mb) / 2})">Training Time (s)</text>')
+    o.append(f'<text x="16" y="{(mt + h - mb) / 2}" text-anchor="middle" transform="rotate(-90 16 {(mt + h - mb) / 2})">{ylabel}</text>')
     for i, (tr, (k, v, sd)) in enumerate(series.items()):
         c = colors[i % len(colors)]
         pts = " ".join(f"{sx(x):.1f},{sy(y):.1f}" for x, y in zip(k, v))
+        if len(k) == 1 and len(series) > 1:      # the single-rank baseline: dashed, across the plot
+            o.append(f'<line x1="{ml}" y1="{sy(v[0]):.1f}" x2="{w - mr}" y2="{sy(v[0]):.1f}" stroke="{c}" stroke-dasharray="6 4"/>')
         o.append(f'<polyline points="{pts}" fill="none" stroke="{c}" stroke-width="2"/>')
         for x, y, e in zip(k, v, sd):
             o.append(f'<circle cx="{sx(x):.1f}" cy="{sy(y):.1f}" r="3.5" fill="{c}"/>')
@@ -154,13 +161,14 @@ def main():
     ap.add_argument("files", nargs="+")
     ap.add_argument("--plot", default=None)
     ap.add_argument("--network", action="store_true")
+    ap.add_argument("--metric", default="seconds", choices=["seconds", "memory"], help="what --plot draws (Experiments.ipynb plots both)")
     ap.add_argument("--rule", default="delay", choices=["delay", "loss"],
                     help="--network: which rule type to tabulate (Experiments_network.ipynb plots both)")
     a = ap.parse_args()
     rows = load(a.files)
     print(table(rows, a.network, a.rule))
     if a.plot:
-        plot(rows, a.plot, a.network, a.rule)
+        plot(rows, a.plot, a.network, a.rule, a.metric)
 
 
 if __name__ == "__main__":

@@ -99,3 +99,21 @@ def test_deploy_assets_and_launcher_auto(tmp_path):
     cp = subprocess.run([sys.executable, "-m", "pytorch_distributed_rnn_b200.parallel.launch", "-n", "auto", str(script)],
                         capture_output=True, text=True, cwd=ROOT, env={**__import__("os").environ, "CUDA_VISIBLE_DEVICES": ""})
     assert cp.returncode == 0 and cp.stdout.strip() == "rank 0 of 1", cp.stderr
+
+
+def test_analysis_memory_plot_and_local_baseline(tmp_path):
+    """A1 (evaluation/Experiments.ipynb): time AND memory vs ranks per trainer, the local run as a dashed baseline."""
+    import analysis
+    rows = [dict(trainer="local", ranks=1, batch=1440, seconds=1.0, memory=800.0, samples=6912, rule_type=None, rule_value=None)]
+    for n, s_, m in ((1, 1.1, 900.0), (2, 0.6, 950.0), (4, 0.35, 990.0)):
+        for rep in (0.0, 0.02):
+            rows.append(dict(trainer="distributed", ranks=n, batch=1440, seconds=s_ + rep, memory=m, samples=6912,
+                             rule_type=None, rule_value=None))
+    t = analysis.table(rows)
+    assert "| distributed | 2 | 1440 | 0.6100 |" in t and "| 2 | 0.0141 |" in t          # mean and sd over the repeats
+    out_t = Path(analysis.plot(rows, tmp_path / "t.png"))
+    out_m = Path(analysis.plot(rows, tmp_path / "m.png", metric="memory"))
+    assert out_t.exists() and out_m.exists()
+    if out_t.suffix == ".svg":     # the dependency-free renderer: check what it drew
+        svg_t, svg_m = out_t.read_text(), out_m.read_text()
+        assert "stroke-dasharray" in svg_t and "Training Time (s)" in svg_t and "Memory (MiB)" in svg_m
